@@ -26,7 +26,7 @@ extern "C" {
 #endif
 
 #define RT_ARENA_MAGIC 0x4152545242323030ull /* "00B2RTRA" */
-#define RT_ARENA_VERSION 3u
+#define RT_ARENA_VERSION 4u
 #define RT_ARENA_ALIGN 16u
 
 /* section ids */
@@ -115,6 +115,8 @@ typedef struct rt_material {
 	int32_t index_tex;
 	int32_t refl, trans, recur; /* Material::_refl/_trans/_recur with indeterminate pinned to 0 */
 	int32_t pad[3];
+	double shininess_raw;   /* MaterialParameter::_value[0] of _shininess / _index: what per-vertex material */
+	double index_raw;       /* interpolation (trimesh.cpp:157-163, material.h:177-189,281-293) sums before intensityValue */
 } rt_material;
 
 typedef struct rt_texture {

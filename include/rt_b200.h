@@ -1,0 +1,140 @@
+/* rt_b200.h - C-ABI of the B200 device path for the CS378H ray tracer's per-pixel trace loop.
+ *
+ * This is the drop-in boundary.  The reference has no FFI layer: its callers use
+ * the C++ class RayTracer (reference ray/src/RayTracer.h:26-75).  Every entry point below names
+ * the RayTracer member (or the piece of scene loading) it replaces; the host class
+ * cs378hgraphics_raytracer_b200/csrc/host/RayTracer.h keeps the reference's member names and
+ * forwards to these functions.  Plain pointers and sizes only; no C++/torch types; nothing
+ * throws across this boundary.  All calls are synchronous: results are complete on return
+ * (the reference's checkRender() is `return true`, RayTracer.cpp:372-375).
+ *
+ * There is NO CPU fallback behind this header: without a CUDA device rt_create fails.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "rt_arena.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t rt_status;
+enum {
+	RT_OK = 0,
+	RT_ERR_ARG = 1,      /* null pointer, bad size, bad arena */
+	RT_ERR_CUDA = 2,     /* a CUDA runtime call failed (message in rt_last_error) */
+	RT_ERR_NO_DEVICE = 3,/* no usable CUDA device: there is no CPU path */
+	RT_ERR_NO_SCENE = 4, /* render/trace before rt_upload_scene */
+	RT_ERR_IO = 5,       /* scene / texture file could not be read */
+	RT_ERR_PARSE = 6,    /* .ray syntax or semantic error (message in rt_host_last_error) */
+	RT_ERR_OVERFLOW = 7, /* a device work queue overflowed (never expected; reported, not hidden) */
+	RT_ERR_UNSUPPORTED = 8
+};
+
+/* Render settings: the POD image of the reference's global `traceUI` getters that the hot loop
+ * reads (reference ray/src/ui/TraceUI.h:35-129; set by CommandLineUI.cpp:30-131). */
+enum { RT_AA_NONE = 0, RT_AA_SUPERSAMPLE = 1, RT_AA_ADAPTIVE = 2, RT_AA_JITTERED = 3 };
+typedef struct rt_params {
+	int32_t depth;               /* getDepth(): -r, default 0 */
+	int32_t aa_mode;             /* getAAMode(): -O r|a|j */
+	int32_t aa_samples;          /* getAASamples(): -A after -O r|a|j, default 3 */
+	int32_t dof_on;              /* dofSwitch(): -O d */
+	int32_t dof_divs;            /* getDofSubDiv(): -B after -O d, default 5 */
+	int32_t anaglyph;            /* anaglyph(): -O g */
+	int32_t overlapping_objects; /* overlappingObjects(): -O o */
+	int32_t use_cubemap;         /* cubeMap(): needs a cube map in the arena as well */
+	int32_t soft_shadow_res;     /* softShadowRes(): -O s -A n, default 5 */
+	int32_t pad;
+	double aterm_thresh;         /* getATermThresh(): -O c -A thr; aTermSwitch() is thresh > 0 */
+	double aa_thresh;            /* getAAThresh(): -B after -O a, default 1.0 */
+	double dof_fd;               /* getDofFD(): default 3 */
+	double dof_apsz;             /* getDofApSz(): default 0.05 */
+} rt_params;
+
+/* Fills the reference's defaults (TraceUI.h:37-129). */
+void rt_params_default(rt_params* p);
+
+typedef struct rt_ray {
+	double p[3];
+	double d[3];
+} rt_ray;
+
+/* What Scene::intersect leaves in an isect (reference scene.cpp:157-180), with the object
+ * pointer replaced by indices: obj = position in Scene::objects, face = position in
+ * Trimesh::faces (non-degenerate faces only) or -1; a miss is obj = face = -1, t = 1000.0. */
+typedef struct rt_hit {
+	int32_t obj;
+	int32_t face;
+	double t;
+	double N[3];
+} rt_hit;
+
+/* Ray counters of one call: camera = Scene::intersect calls made for eye / DOF
+ * lens / AA sample rays, reflection + refraction = the recursive ones, shadow = Scene::
+ * intersectList calls made by Light::srsAttenuation. */
+typedef struct rt_stats {
+	uint64_t camera_rays;
+	uint64_t reflection_rays;
+	uint64_t refraction_rays;
+	uint64_t shadow_rays;
+	double device_ms;  /* CUDA-event time of the device work of this call */
+	uint64_t launches; /* kernels launched by this call */
+} rt_stats;
+
+typedef struct rt_ctx rt_ctx;
+
+/* ---- device context ------------------------------------------------------------------ */
+/* Creates a context on CUDA device `device` (one context = one GPU = one host thread, like one
+ * RayTracer instance). */
+rt_status rt_create(int device, rt_ctx** out);
+void rt_destroy(rt_ctx* ctx);
+const char* rt_last_error(const rt_ctx* ctx);
+
+/* Replaces what RayTracer::loadScene leaves behind for the tracer (RayTracer.cpp:196-240): the
+ * arena (include/rt_arena.h) is validated, copied to HBM and re-laid-out for traversal.  The
+ * caller keeps ownership of `arena`. */
+rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes);
+
+/* RayTracer::traceImage(w,h) + getBuffer (RayTracer.cpp:279-314,184-189): renders the whole
+ * frame into rgb_out (host memory, w*h*3 bytes, row 0 = bottom scan line like RayTracer::buffer).
+ * rt_render_tiles renders only the 32x32-pixel tiles t with t % n_parts == part (interleaved
+ * tile partition used for multi-GPU); other pixels of rgb_out are left untouched. */
+rt_status rt_render(rt_ctx* ctx, const rt_params* p, int w, int h, uint8_t* rgb_out, rt_stats* stats);
+rt_status rt_render_tiles(rt_ctx* ctx, const rt_params* p, int w, int h, int part, int n_parts,
+                          uint8_t* rgb_out, rt_stats* stats);
+/* Same work with the frame left in HBM: *dev_rgb receives a device pointer owned by the context
+ * (valid until the next render call).  Used by the multi-GPU gather and by device-resident timing. */
+rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int part, int n_parts,
+                           void** dev_rgb, rt_stats* stats);
+
+/* RayTracer::tracePixel(i,j) for n pixels (RayTracer.cpp:81-102): rgb_out[3n] doubles, clamped
+ * like the reference, not quantised.  ij = {i0,j0,i1,j1,...}. */
+rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const int32_t* ij, int n,
+                          double* rgb_out);
+
+/* RayTracer::traceRay(r, thresh, depth, t) for n rays (RayTracer.cpp:108-174): hits_out[n] is the
+ * Scene::intersect result of each ray itself, rgb_out[3n] the returned colour (either may be NULL). */
+rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int n, int depth,
+                        rt_hit* hits_out, double* rgb_out);
+
+/* ---- host-side scene loading (no GPU needed) -------------------------------------------- */
+/* Replaces Tokenizer + Parser::parseScene + Scene::add/conclude + Trimesh::conclude (reference
+ * parser/Parser.cpp:26-95, scene.cpp:133-153, trimesh.cpp:69-77, kdTree.h:23-78): parses a .ray
+ * file, builds the reference's own trees and emits the arena.  cubemap_faces is NULL or six image
+ * paths in +x -x +y -y +z -z order (what TraceUI::smartLoadCubemap resolves, TraceUI.cc:148-167).
+ * The arena is malloc'ed; free it with rt_arena_free. */
+rt_status rt_load_ray_file(const char* path, const char* const* cubemap_faces, void** arena_out,
+                           size_t* bytes_out);
+void rt_arena_free(void* arena);
+/* Message of the last failed rt_load_ray_file on this thread. */
+const char* rt_host_last_error(void);
+/* Checks magic, version, section table and index ranges of an arena. */
+rt_status rt_arena_validate(const void* arena, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

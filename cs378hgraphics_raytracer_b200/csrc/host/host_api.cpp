@@ -1,0 +1,139 @@
+// host_api.cpp - the host-only half of the C-ABI (include/rt_b200.h): scene loading, arena
+// validation, default settings.  No CUDA here; the device half is ../rt_api.cu.
+#include <cstdlib>
+#include <cstring>
+#include <exception>
+#include <string>
+#include "ray_scene.hpp"
+#include "rt_arena_writer.hpp"
+#include "rt_b200.h"
+
+static thread_local std::string g_host_error;
+
+extern "C" {
+
+void rt_params_default(rt_params* p)
+{
+	if (!p) return;
+	std::memset(p, 0, sizeof(*p));
+	p->depth = 0;            // TraceUI.h:41
+	p->aa_mode = RT_AA_NONE; // :60
+	p->aa_samples = 3;       // :61
+	p->aa_thresh = 1.0;      // :62
+	p->aterm_thresh = 0.0;   // :51
+	p->dof_on = 0;           // :110
+	p->dof_apsz = 0.05;      // :111
+	p->dof_divs = 5;         // :112
+	p->dof_fd = 3.0;         // :113
+	p->soft_shadow_res = 5;  // :129
+}
+
+rt_status rt_load_ray_file(const char* path, const char* const* cubemap_faces, void** arena_out, size_t* bytes_out)
+{
+	if (!path || !arena_out || !bytes_out) { g_host_error = "null argument"; return RT_ERR_ARG; }
+	*arena_out = nullptr;
+	*bytes_out = 0;
+	try {
+		rs::Scene sc;
+		if (cubemap_faces) {
+			for (int k = 0; k < 6; k++) {
+				if (!cubemap_faces[k]) { g_host_error = "cubemap needs six face files"; return RT_ERR_ARG; }
+				sc.cubemap[k] = rs::load_texture(sc, cubemap_faces[k]);
+			}
+			sc.has_cubemap = true;
+		}
+		rs::parse_ray_file(path, sc);
+		if (sc.objects.empty()) { g_host_error = "scene has no geometry"; return RT_ERR_PARSE; }
+		void* a = rs::flatten(sc, bytes_out);
+		if (!a) { g_host_error = "out of memory"; return RT_ERR_IO; }
+		*arena_out = a;
+		return RT_OK;
+	} catch (const std::exception& e) {
+		g_host_error = e.what();
+		const bool io = g_host_error.find("couldn't read") != std::string::npos || g_host_error.find("Unable to load") != std::string::npos;
+		return io ? RT_ERR_IO : RT_ERR_PARSE;
+	} catch (...) {
+		g_host_error = "unknown error";
+		return RT_ERR_PARSE;
+	}
+}
+
+void rt_arena_free(void* arena) { std::free(arena); }
+
+const char* rt_host_last_error(void) { return g_host_error.c_str(); }
+
+static const uint32_t kElemSize[RT_SEC_MAX] = {
+	0, sizeof(rt_camera), sizeof(rt_globals), sizeof(rt_light), sizeof(rt_material), sizeof(rt_texture), 1,
+	sizeof(rt_object), sizeof(rt_node), 4, sizeof(rt_mesh), sizeof(rt_node), 4, sizeof(rt_face), 24, 24, 4};
+
+static bool tree_ok(const rt_node* n, uint64_t n_nodes, uint64_t n_items, uint64_t item_limit, const int32_t* items)
+{
+	for (uint64_t k = 0; k < n_nodes; k++) {
+		if (n[k].right >= 0) {
+			if ((uint64_t)n[k].right >= n_nodes || (uint64_t)n[k].right <= k + 1) return false;
+		} else {
+			if (n[k].first < 0 || n[k].count < 0 || (uint64_t)n[k].first + n[k].count > n_items) return false;
+			for (int32_t i = 0; i < n[k].count; i++)
+				if (items[n[k].first + i] < 0 || (uint64_t)items[n[k].first + i] >= item_limit) return false;
+		}
+	}
+	return true;
+}
+
+rt_status rt_arena_validate(const void* arena, size_t bytes)
+{
+	if (!arena || bytes < sizeof(rt_arena_header)) return RT_ERR_ARG;
+	rt::ArenaView A(arena);
+	const rt_arena_header* h = A.hdr;
+	if (h->magic != RT_ARENA_MAGIC || h->version != RT_ARENA_VERSION || h->n_sections != RT_SEC_MAX || h->total_bytes != bytes) return RT_ERR_ARG;
+	for (uint32_t s = 1; s < RT_SEC_MAX; s++) {
+		const rt_section& sec = h->sections[s];
+		if (sec.id != s || sec.elem_size != kElemSize[s] || sec.offset % RT_ARENA_ALIGN) return RT_ERR_ARG;
+		if (sec.offset > bytes || sec.count > (bytes - sec.offset) / (sec.elem_size ? sec.elem_size : 1)) return RT_ERR_ARG;
+	}
+	if (A.count(RT_SEC_CAMERA) != 1 || A.count(RT_SEC_GLOBALS) != 1) return RT_ERR_ARG;
+	const uint64_t n_obj = A.count(RT_SEC_OBJECTS), n_mat = A.count(RT_SEC_MATERIALS), n_tex = A.count(RT_SEC_TEXTURES);
+	const uint64_t n_mesh = A.count(RT_SEC_MESHES);
+	if (n_obj == 0 || n_obj > 0x3fffffffull) return RT_ERR_ARG;
+	const rt_globals* g = A.ptr<rt_globals>(RT_SEC_GLOBALS);
+	if ((uint64_t)g->n_objects != n_obj || (uint64_t)g->n_lights != A.count(RT_SEC_LIGHTS)) return RT_ERR_ARG;
+	for (int k = 0; k < 6; k++)
+		if (g->has_cubemap && (g->cubemap[k] < 0 || (uint64_t)g->cubemap[k] >= n_tex)) return RT_ERR_ARG;
+	const rt_texture* tx = A.ptr<rt_texture>(RT_SEC_TEXTURES);
+	for (uint64_t k = 0; k < n_tex; k++)
+		if (tx[k].width <= 0 || tx[k].height <= 0 || tx[k].offset + (uint64_t)tx[k].width * tx[k].height * 3 > A.count(RT_SEC_TEXDATA)) return RT_ERR_ARG;
+	const rt_material* mt = A.ptr<rt_material>(RT_SEC_MATERIALS);
+	for (uint64_t k = 0; k < n_mat; k++) {
+		for (int p = 0; p < RT_NPARAM; p++)
+			if (mt[k].tex[p] >= (int64_t)n_tex) return RT_ERR_ARG;
+		if (mt[k].shininess_tex >= (int64_t)n_tex || mt[k].index_tex >= (int64_t)n_tex) return RT_ERR_ARG;
+	}
+	const rt_object* ob = A.ptr<rt_object>(RT_SEC_OBJECTS);
+	for (uint64_t k = 0; k < n_obj; k++) {
+		if (ob[k].type < 0 || ob[k].type > RT_OBJ_TRIMESH || ob[k].material < 0 || (uint64_t)ob[k].material >= n_mat) return RT_ERR_ARG;
+		if (ob[k].type == RT_OBJ_TRIMESH && (ob[k].mesh < 0 || (uint64_t)ob[k].mesh >= n_mesh)) return RT_ERR_ARG;
+	}
+	if (!tree_ok(A.ptr<rt_node>(RT_SEC_SCENE_NODES), A.count(RT_SEC_SCENE_NODES), A.count(RT_SEC_SCENE_ITEMS), n_obj, A.ptr<int32_t>(RT_SEC_SCENE_ITEMS)))
+		return RT_ERR_ARG;
+	const rt_mesh* ms = A.ptr<rt_mesh>(RT_SEC_MESHES);
+	const rt_face* fc = A.ptr<rt_face>(RT_SEC_FACES);
+	for (uint64_t k = 0; k < n_mesh; k++) {
+		const rt_mesh& m = ms[k];
+		if (m.node_off + m.node_cnt > A.count(RT_SEC_MESH_NODES) || m.item_off + m.item_cnt > A.count(RT_SEC_MESH_ITEMS)) return RT_ERR_ARG;
+		if (m.face_off + m.face_cnt > A.count(RT_SEC_FACES) || m.vert_off + m.vert_cnt > A.count(RT_SEC_VERTS)) return RT_ERR_ARG;
+		if (m.vnorm_off >= 0 && (uint64_t)m.vnorm_off + m.vert_cnt > A.count(RT_SEC_VNORMALS)) return RT_ERR_ARG;
+		if (m.vmat_off >= 0 && (uint64_t)m.vmat_off + m.vert_cnt > A.count(RT_SEC_VMATS)) return RT_ERR_ARG;
+		if (m.object < 0 || (uint64_t)m.object >= n_obj || m.node_cnt == 0) return RT_ERR_ARG;
+		for (uint64_t f = 0; f < m.face_cnt; f++)
+			for (int v = 0; v < 3; v++)
+				if (fc[m.face_off + f].ids[v] < 0 || (uint64_t)fc[m.face_off + f].ids[v] >= m.vert_cnt) return RT_ERR_ARG;
+		if (!tree_ok(A.ptr<rt_node>(RT_SEC_MESH_NODES) + m.node_off, m.node_cnt, m.item_cnt, m.face_cnt, A.ptr<int32_t>(RT_SEC_MESH_ITEMS) + m.item_off))
+			return RT_ERR_ARG;
+	}
+	const int32_t* vm = A.ptr<int32_t>(RT_SEC_VMATS);
+	for (uint64_t k = 0; k < A.count(RT_SEC_VMATS); k++)
+		if (vm[k] < 0 || (uint64_t)vm[k] >= n_mat) return RT_ERR_ARG;
+	return RT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,77 @@
+// rt_derive.hpp - host-side preparation of the traversal layouts derived from an arena
+// (rt_scene.cuh): the per-leaf-item triangle records and the pruning slacks.  Used by
+// rt_api.cu before the upload (and by tests/hostsim to run the same per-ray code on the CPU).
+#pragma once
+#include <cmath>
+#include <vector>
+#include "rt_arena_writer.hpp"
+#include "rt_scene.cuh"
+
+namespace rtd {
+
+struct Derived {
+	std::vector<DTri> tris;
+	std::vector<double> mesh_slack;
+	double scene_slack = 1e-9;
+	int max_scene_depth = 0, max_mesh_depth = 0;
+};
+
+inline int tree_depth(const rt_node* n, uint64_t cnt)
+{
+	// pre-order array: depth of node k = number of open ancestors
+	std::vector<int> depth(cnt, 0);
+	int best = cnt ? 1 : 0;
+	for (uint64_t k = 0; k < cnt; k++) {
+		if (k == 0) depth[0] = 1;
+		if (n[k].right >= 0) {
+			depth[k + 1] = depth[k] + 1;
+			depth[n[k].right] = depth[k] + 1;
+			if (depth[k] + 1 > best) best = depth[k] + 1;
+		}
+	}
+	return best;
+}
+
+inline double box_extent(const rt_node& n)
+{
+	double m = 1.0;
+	for (int a = 0; a < 3; a++) {
+		if (std::fabs(n.bmin[a]) > m) m = std::fabs(n.bmin[a]);
+		if (std::fabs(n.bmax[a]) > m) m = std::fabs(n.bmax[a]);
+	}
+	return m;
+}
+
+inline void derive(const rt::ArenaView& A, Derived& D)
+{
+	const rt_mesh* meshes = A.ptr<rt_mesh>(RT_SEC_MESHES);
+	const rt_face* faces = A.ptr<rt_face>(RT_SEC_FACES);
+	const double* verts = A.ptr<double>(RT_SEC_VERTS);
+	const int32_t* mitems = A.ptr<int32_t>(RT_SEC_MESH_ITEMS);
+	const rt_node* mnodes = A.ptr<rt_node>(RT_SEC_MESH_NODES);
+	D.tris.resize(A.count(RT_SEC_MESH_ITEMS));
+	D.mesh_slack.resize(A.count(RT_SEC_MESHES));
+	for (uint64_t m = 0; m < A.count(RT_SEC_MESHES); m++) {
+		const rt_mesh& M = meshes[m];
+		for (uint64_t k = 0; k < M.item_cnt; k++) {
+			const rt_face& f = faces[M.face_off + mitems[M.item_off + k]];
+			DTri& T = D.tris[M.item_off + k];
+			for (int c = 0; c < 3; c++) {
+				T.v0[c] = verts[3 * (M.vert_off + f.ids[0]) + c];
+				T.v1[c] = verts[3 * (M.vert_off + f.ids[1]) + c];
+				T.v2[c] = verts[3 * (M.vert_off + f.ids[2]) + c];
+				T.n[c] = f.normal[c];
+			}
+		}
+		// slack: far above the rounding of a computed hit point (ulp(extent) ~ 2e-16*extent),
+		// far below any geometric feature
+		D.mesh_slack[m] = 1e-9 * box_extent(mnodes[M.node_off]);
+		int d = tree_depth(mnodes + M.node_off, M.node_cnt);
+		if (d > D.max_mesh_depth) D.max_mesh_depth = d;
+	}
+	const rt_node* snodes = A.ptr<rt_node>(RT_SEC_SCENE_NODES);
+	D.scene_slack = 1e-9 * box_extent(snodes[0]);
+	D.max_scene_depth = tree_depth(snodes, A.count(RT_SEC_SCENE_NODES));
+}
+
+} // namespace rtd

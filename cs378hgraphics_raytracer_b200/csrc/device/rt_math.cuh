@@ -1,0 +1,72 @@
+// rt_math.cuh - FP64 vector helpers for the device path, in glm 0.9.8.4's evaluation order.
+//
+// Everything on the hit-decision path of the reference is double precision glm arithmetic built
+// for baseline x86-64 (no FMA contraction).  To select the same hit primitives bit for bit, the
+// device code spells every expression term by term in the same association order (SURVEY.md
+// Appendix B) and this translation unit is compiled with -fmad=false, IEEE division and sqrt
+// (nvcc defaults --prec-div=true --prec-sqrt=true for FP64).
+//
+// RT_HD functions also compile as plain C++ (g++ -ffp-contract=off) so that tests can single-step
+// the same per-ray code on the CPU next to the reference (tests/hostsim); the product library
+// never contains that host build.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define RT_HD __host__ __device__ __forceinline__
+#define RT_HDN __host__ __device__ __noinline__
+#else
+#define RT_HD inline
+#define RT_HDN inline
+#endif
+
+namespace rtd {
+
+struct d3 {
+	double x, y, z;
+};
+struct d2 {
+	double x, y;
+};
+
+RT_HD d3 mk3(double x, double y, double z) { d3 r; r.x = x; r.y = y; r.z = z; return r; }
+RT_HD d3 ld3(const double* p) { return mk3(p[0], p[1], p[2]); }
+RT_HD d3 operator+(d3 a, d3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+RT_HD d3 operator-(d3 a, d3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+RT_HD d3 operator*(d3 a, d3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
+RT_HD d3 operator*(d3 a, double s) { return mk3(a.x * s, a.y * s, a.z * s); }
+RT_HD d3 operator*(double s, d3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
+RT_HD d3 operator-(d3 a) { return mk3(-a.x, -a.y, -a.z); }
+RT_HD double comp(const d3& v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : v.z); }
+
+RT_HD double dot(d3 a, d3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+RT_HD double length(d3 a) { return sqrt(dot(a, a)); }
+RT_HD d3 normalize(d3 a) { return a * (1.0 / sqrt(dot(a, a))); }
+RT_HD d3 cross(d3 a, d3 b) { return mk3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
+RT_HD double gmin(double x, double y) { return (y < x) ? y : x; }
+RT_HD double gmax(double x, double y) { return (x < y) ? y : x; }
+RT_HD double gclamp(double x, double lo, double hi) { return gmin(gmax(x, lo), hi); }
+RT_HD d3 gclamp(d3 v, double lo, double hi) { return mk3(gclamp(v.x, lo, hi), gclamp(v.y, lo, hi), gclamp(v.z, lo, hi)); }
+RT_HD d3 vpow(d3 b, double e) { return mk3(pow(b.x, e), pow(b.y, e), pow(b.z, e)); }
+
+// reference scene.h:57-62 on a column-major dmat4 m[col*4+row]: (x,y,z,1) in, xyz out;
+// glm mat4*vec4 = (m0*v0 + m1*v1) + (m2*v2 + m3*v3)
+RT_HD d3 xform_point(const double* m, d3 v)
+{
+	return mk3((m[0] * v.x + m[4] * v.y) + (m[8] * v.z + m[12] * 1.0),
+	           (m[1] * v.x + m[5] * v.y) + (m[9] * v.z + m[13] * 1.0),
+	           (m[2] * v.x + m[6] * v.y) + (m[10] * v.z + m[14] * 1.0));
+}
+// glm mat3*vec3 on a column-major dmat3 m[col*3+row]
+RT_HD d3 mul33(const double* m, d3 v)
+{
+	return mk3(m[0] * v.x + m[3] * v.y + m[6] * v.z,
+	           m[1] * v.x + m[4] * v.y + m[7] * v.z,
+	           m[2] * v.x + m[5] * v.y + m[8] * v.z);
+}
+
+#define RT_RAY_EPSILON 0.00000001
+#define RT_EPS32 (RT_RAY_EPSILON / 32)
+
+} // namespace rtd

@@ -1,0 +1,241 @@
+// rt_prims.cuh - bounding-box slab test and the analytic primitives, closest-hit variants.
+// Each function restates the reference member it cites, comparison for comparison.
+#pragma once
+#include "rt_scene.cuh"
+
+namespace rtd {
+
+// BoundingBox::intersect (reference ray/src/scene/bbox.cc:33-70).  The per-axis early returns
+// are monotone (tMin only grows, tMax only shrinks) so testing once after the loop is identical.
+// `entry` receives tMin lowered by sl = slack/|d| per axis (precomputed per ray): a conservative entry distance used ONLY to
+// cull subtrees that cannot beat the current closest hit; box membership itself is decided by the
+// reference's exact arithmetic (see DESIGN.md "pruning without changing the winner").
+RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3& d, const d3& sl, double& entry)
+{
+	double tMin = -1.0e308, tMax = 1.0e308, en = -1.0e308;
+#define RT_SLAB(O, D, LO, HI, SL)                      \
+	if (D != 0.0) {                                    \
+		double t1 = (LO - O) / D, t2 = (HI - O) / D;   \
+		if (t1 > t2) { double tt = t1; t1 = t2; t2 = tt; } \
+		if (t1 > tMin) tMin = t1;                      \
+		if (t2 < tMax) tMax = t2;                      \
+		double e = t1 - SL;                            \
+		if (e > en) en = e;                            \
+	}
+	RT_SLAB(o.x, d.x, bmin[0], bmax[0], sl.x)
+	RT_SLAB(o.y, d.y, bmin[1], bmax[1], sl.y)
+	RT_SLAB(o.z, d.z, bmin[2], bmax[2], sl.z)
+#undef RT_SLAB
+	entry = en;
+	if (tMin > tMax) return false;
+	if (tMax < RT_RAY_EPSILON) return false;
+	return true;
+}
+
+// What a primitive's intersectLocal leaves in the isect (object space).
+struct LocalHit {
+	double t;
+	d3 N;
+	d2 uv;
+};
+
+// Sphere::intersectLocal (reference SceneObjects/Sphere.cpp:9-40).  It re-normalises the already
+// normalised direction (:10), which can move it by an ulp, so that is reproduced.
+template <bool FULL> RT_HD bool sphere_hit(d3 o, d3 d, LocalHit& h)
+{
+	d = normalize(d);
+	d3 v = -o;
+	double b = dot(v, d);
+	double disc = b * b - dot(v, v) + 1;
+	if (disc < 0.0) return false;
+	disc = sqrt(disc);
+	double t2 = b + disc;
+	if (t2 <= RT_RAY_EPSILON) return false;
+	double t1 = b - disc;
+	double t = (t1 > RT_RAY_EPSILON) ? t1 : t2;
+	h.t = t;
+	if (FULL) h.N = normalize(o + t * d);
+	return true;
+}
+
+// Box::intersectLocal (reference SceneObjects/Box.cpp:11-64).  The bump-mapped normal
+// (Box::computeNormal :99-108) needs the material and is applied by the caller from `face`.
+template <bool FULL> RT_HD bool box_prim_hit(d3 o, d3 d, LocalHit& h, int& face)
+{
+	double bestT = 1e100;
+	int best = -1;
+#pragma unroll
+	for (int it = 0; it < 6; it++) {
+		const int m0 = it % 3, m1 = (it + 1) % 3, m2 = (it + 2) % 3;
+		const double dm = comp(d, m0);
+		if (dm == 0) continue;
+		const double t = ((it / 3) - 0.5 - comp(o, m0)) / dm;
+		if (t < RT_RAY_EPSILON || t > bestT) continue;
+		const double x = comp(o, m1) + t * comp(d, m1);
+		const double y = comp(o, m2) + t * comp(d, m2);
+		if (x <= 0.5 && x >= -0.5 && y <= 0.5 && y >= -0.5) {
+			if (bestT > t) { bestT = t; best = it; }
+		}
+	}
+	if (best < 0) return false;
+	h.t = bestT;
+	face = best;
+	if (FULL) {
+		d3 P = o + bestT * d;
+		const int i1 = (best + 1) % 3, i2 = (best + 2) % 3;
+		const int lo = i1 < i2 ? i1 : i2, hi = i1 < i2 ? i2 : i1;
+		if (best < 3) { h.uv.x = 0.5 - comp(P, lo); h.uv.y = 0.5 + comp(P, hi); }
+		else { h.uv.x = 0.5 + comp(P, lo); h.uv.y = 0.5 + comp(P, hi); }
+		if (best < 3) h.N = mk3(-(double)(best == 0), -(double)(best == 1), -(double)(best == 2));
+		else h.N = mk3((double)(best == 3), (double)(best == 4), (double)(best == 5));
+	}
+	return true;
+}
+
+// Square::intersectLocal (reference SceneObjects/Square.cpp:9-46)
+template <bool FULL> RT_HD bool square_hit(d3 o, d3 d, LocalHit& h)
+{
+	if (d.z == 0.0) return false;
+	double t = -o.z / d.z;
+	if (t <= RT_RAY_EPSILON) return false;
+	d3 P = o + t * d;
+	if (P.x < -0.5 || P.x > 0.5) return false;
+	if (P.y < -0.5 || P.y > 0.5) return false;
+	h.t = t;
+	if (FULL) {
+		h.N = (d.z > 0.0) ? mk3(0.0, 0.0, -1.0) : mk3(0.0, 0.0, 1.0);
+		h.uv.x = P.x + 0.5;
+		h.uv.y = P.y + 0.5;
+	}
+	return true;
+}
+
+// Cylinder::intersectBody (reference SceneObjects/Cylinder.cpp:30-93); capped is always true
+// (Cylinder.h:11) so the normal flip for the uncapped case never runs.
+template <bool FULL> RT_HD bool cyl_body(d3 o, d3 d, LocalHit& h)
+{
+	double x0 = o.x, y0 = o.y, x1 = d.x, y1 = d.y;
+	double a = x1 * x1 + y1 * y1;
+	double b = 2.0 * (x0 * x1 + y0 * y1);
+	double c = x0 * x0 + y0 * y0 - 1.0;
+	if (0.0 == a) return false;
+	double disc = b * b - 4.0 * a * c;
+	if (disc < 0.0) return false;
+	disc = sqrt(disc);
+	double t2 = (-b + disc) / (2.0 * a);
+	if (t2 <= RT_RAY_EPSILON) return false;
+	double t1 = (-b - disc) / (2.0 * a);
+	if (t1 > RT_RAY_EPSILON) {
+		d3 P = o + t1 * d;
+		if (P.z >= 0.0 && P.z <= 1.0) {
+			h.t = t1;
+			if (FULL) h.N = normalize(mk3(P.x, P.y, 0.0));
+			return true;
+		}
+	}
+	d3 P = o + t2 * d;
+	if (P.z >= 0.0 && P.z <= 1.0) {
+		h.t = t2;
+		if (FULL) h.N = normalize(mk3(P.x, P.y, 0.0));
+		return true;
+	}
+	return false;
+}
+
+// Cylinder::intersectCaps (reference SceneObjects/Cylinder.cpp:95-153)
+template <bool FULL> RT_HD bool cyl_caps(d3 o, d3 d, LocalHit& h)
+{
+	double pz = o.z, dz = d.z;
+	if (0.0 == dz) return false;
+	double t1, t2;
+	if (dz > 0.0) { t1 = (-pz) / dz; t2 = (1.0 - pz) / dz; }
+	else { t1 = (1.0 - pz) / dz; t2 = (-pz) / dz; }
+	if (t2 < RT_RAY_EPSILON) return false;
+	if (t1 >= RT_RAY_EPSILON) {
+		d3 p = o + t1 * d;
+		if ((p.x * p.x + p.y * p.y) <= 1.0) {
+			h.t = t1;
+			if (FULL) h.N = (dz > 0.0) ? mk3(0.0, 0.0, -1.0) : mk3(0.0, 0.0, 1.0);
+			return true;
+		}
+	}
+	d3 p = o + t2 * d;
+	if ((p.x * p.x + p.y * p.y) <= 1.0) {
+		h.t = t2;
+		if (FULL) h.N = (dz > 0.0) ? mk3(0.0, 0.0, 1.0) : mk3(0.0, 0.0, -1.0);
+		return true;
+	}
+	return false;
+}
+
+// Cylinder::intersectLocal (reference SceneObjects/Cylinder.cpp:8-28): caps first, the body
+// replaces them only when strictly closer.
+template <bool FULL> RT_HD bool cylinder_hit(d3 o, d3 d, LocalHit& h)
+{
+	if (cyl_caps<FULL>(o, d, h)) {
+		LocalHit b;
+		if (cyl_body<FULL>(o, d, b)) {
+			if (b.t < h.t) { h.t = b.t; if (FULL) h.N = b.N; }
+		}
+		return true;
+	}
+	return cyl_body<FULL>(o, d, h);
+}
+
+// Cone::intersectLocal (reference SceneObjects/Cone.cpp:7-107), root bookkeeping kept literal.
+// prm = {height, b_radius, t_radius, beta_squared, gamma}
+template <bool FULL> RT_HD bool cone_hit(d3 R0, d3 Rd, const double* prm, int capped, LocalHit& h)
+{
+	const double height = prm[0], b_radius = prm[1], t_radius = prm[2], beta_squared = prm[3], gamma = prm[4];
+	d3 normal = mk3(0.0, 0.0, 0.0);
+	double pz = R0.z, dz = Rd.z;
+	double a = Rd.x * Rd.x + Rd.y * Rd.y - beta_squared * Rd.z * Rd.z;
+	if (a == 0.0) return false;
+	double b = 2 * (R0.x * Rd.x + R0.y * Rd.y - beta_squared * ((R0.z + gamma) * Rd.z));
+	double c = -beta_squared * (gamma + R0.z) * (gamma + R0.z) + R0.x * R0.x + R0.y * R0.y;
+	double disc = b * b - 4 * a * c;
+	double theRoot = RT_RAY_EPSILON;
+	if (disc <= 0) return false;
+	disc = sqrt(disc);
+	double nearRoot = (-b + disc) / (2 * a);
+	double farRoot = (-b - disc) / (2 * a);
+	d3 Pn = R0 + nearRoot * Rd;
+	bool nearGood = !(Pn.z < 0 || Pn.z > height);
+	if (nearGood && (nearRoot > theRoot)) {
+		theRoot = nearRoot;
+		d3 P = R0 + theRoot * Rd;
+		normal = mk3(P.x, P.y, -2.0 * beta_squared * (P.z + gamma));
+	}
+	d3 Pf = R0 + farRoot * Rd;
+	bool farGood = !(Pf.z < 0 || Pf.z > height);
+	if (farGood && ((nearGood && farRoot < theRoot) || farRoot > RT_RAY_EPSILON)) {
+		theRoot = farRoot;
+		d3 P = R0 + theRoot * Rd;
+		normal = mk3(P.x, P.y, -2.0 * beta_squared * (P.z + gamma));
+	}
+	if (!capped && dot(normal, Rd) > 0) normal = -normal;
+	double t1 = (-pz) / dz;
+	double t2 = (height - pz) / dz;
+	if (capped) {
+		d3 p = R0 + t1 * Rd;
+		if (p.x * p.x + p.y * p.y <= b_radius * b_radius) {
+			if (t1 < theRoot && t1 > RT_RAY_EPSILON) {
+				theRoot = t1;
+				normal = (dz > 0.0) ? mk3(0.0, 0.0, -1.0) : mk3(0.0, 0.0, 1.0);
+			}
+		}
+		d3 q = R0 + t2 * Rd;
+		if (q.x * q.x + q.y * q.y <= t_radius * t_radius) {
+			if (t2 < theRoot && t2 > RT_RAY_EPSILON) {
+				theRoot = t2;
+				normal = (dz > 0.0) ? mk3(0.0, 0.0, 1.0) : mk3(0.0, 0.0, -1.0);
+			}
+		}
+	}
+	if (theRoot <= RT_RAY_EPSILON) return false;
+	h.t = theRoot;
+	if (FULL) h.N = normalize(normal);
+	return true;
+}
+
+} // namespace rtd

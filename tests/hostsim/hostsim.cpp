@@ -1,0 +1,170 @@
+// hostsim.cpp - TEST INFRASTRUCTURE: compiles the device path's per-ray headers
+// (cs378hgraphics_raytracer_b200/csrc/device/*.cuh) as plain C++ and drives them with a simple
+// CPU loop, so the parity-critical arithmetic (slab test, primitives, ordered traversal with
+// pruning, shadow collection passes, Phong, reflection/refraction spawning) can be checked against
+// the reference oracle in the CPU-only container.  It is NOT part of the product: librt_b200.so
+// contains no host execution path, and nothing outside tests/ loads this library.
+#include <cstring>
+#include <vector>
+#include <omp.h>
+#include "rt_shade.cuh"
+#include "rt_derive.hpp"
+
+using namespace rtd;
+
+namespace {
+struct Sim {
+	DScene S;
+	Derived D;
+};
+
+void setup(Sim& sim, const void* arena)
+{
+	rt::ArenaView A(arena);
+	derive(A, sim.D);
+	DScene& S = sim.S;
+	S.snodes = A.ptr<rt_node>(RT_SEC_SCENE_NODES);
+	S.sitems = A.ptr<int32_t>(RT_SEC_SCENE_ITEMS);
+	S.objs = A.ptr<rt_object>(RT_SEC_OBJECTS);
+	S.meshes = A.ptr<rt_mesh>(RT_SEC_MESHES);
+	S.mesh_slack = sim.D.mesh_slack.data();
+	S.mnodes = A.ptr<rt_node>(RT_SEC_MESH_NODES);
+	S.mitems = A.ptr<int32_t>(RT_SEC_MESH_ITEMS);
+	S.tris = sim.D.tris.data();
+	S.faces = A.ptr<rt_face>(RT_SEC_FACES);
+	S.verts = A.ptr<double>(RT_SEC_VERTS);
+	S.vnormals = A.ptr<double>(RT_SEC_VNORMALS);
+	S.vmats = A.ptr<int32_t>(RT_SEC_VMATS);
+	S.mats = A.ptr<rt_material>(RT_SEC_MATERIALS);
+	S.lights = A.ptr<rt_light>(RT_SEC_LIGHTS);
+	S.texs = A.ptr<rt_texture>(RT_SEC_TEXTURES);
+	S.texdata = A.ptr<uint8_t>(RT_SEC_TEXDATA);
+	S.cam = *A.ptr<rt_camera>(RT_SEC_CAMERA);
+	S.glob = *A.ptr<rt_globals>(RT_SEC_GLOBALS);
+	S.scene_slack = sim.D.scene_slack;
+	S.n_lights = (int)A.count(RT_SEC_LIGHTS);
+	S.n_objs = (int)A.count(RT_SEC_OBJECTS);
+}
+
+template <bool PRUNE> d3 trace_tree(const DScene& S, const rt_params& prm, const RayTask& root, rt_stats* st)
+{
+	std::vector<RayTask> stack;
+	stack.push_back(root);
+	d3 sum = mk3(0, 0, 0);
+	while (!stack.empty()) {
+		RayTask r = stack.back();
+		stack.pop_back();
+		Hit h;
+		RayTask kids[2];
+		int nk;
+		unsigned sh = 0;
+		sum = sum + trace_step<PRUNE>(S, prm, r, h, kids, nk, sh);
+		if (st) {
+			st->shadow_rays += sh;
+			if (r.kind == 0) st->camera_rays++;
+			else if (r.kind == 1) st->reflection_rays++;
+			else st->refraction_rays++;
+		}
+		for (int k = nk - 1; k >= 0; k--) stack.push_back(kids[k]);
+	}
+	return sum;
+}
+
+RayTask make_root(const d3& o, const d3& d, int depth)
+{
+	RayTask r;
+	r.o = o;
+	r.d = d;
+	r.weight = mk3(1, 1, 1);
+	r.att_kt = mk3(1, 1, 1);
+	r.att_mode = 0;
+	r.depth = depth;
+	r.kind = 0;
+	return r;
+}
+
+// RayTracer::trace(x,y) (reference RayTracer.cpp:35-79)
+template <bool PRUNE> d3 sample_colour(const DScene& S, const rt_params& prm, double x, double y, rt_stats* st)
+{
+	const int lenses = prm.dof_on ? prm.dof_divs + 1 : 1;
+	d3 ret = mk3(0, 0, 0);
+	for (int l = 0; l < lenses; l++) {
+		d3 o, d;
+		primary_ray(S.cam, prm, x, y, l, 0.0, o, d);
+		ret = ret + trace_tree<PRUNE>(S, prm, make_root(o, d, prm.depth), st);
+	}
+	if (prm.dof_on) ret = ret * (1.0 / (prm.dof_divs + 1.0));
+	return gclamp(ret, 0.0, 1.0);
+}
+} // namespace
+
+extern "C" {
+
+int sim_trace_rays(const void* arena, const rt_params* prm, const rt_ray* rays, int n, int depth, rt_hit* hits, double* rgb, int prune)
+{
+	Sim sim;
+	setup(sim, arena);
+#pragma omp parallel for schedule(dynamic, 64)
+	for (int k = 0; k < n; k++) {
+		const d3 o = ld3(rays[k].p), d = ld3(rays[k].d);
+		if (hits) {
+			Hit h;
+			bool hit = prune ? closest_hit<true>(sim.S, o, d, h) : closest_hit<false>(sim.S, o, d, h);
+			rt_hit out;
+			out.obj = out.face = -1;
+			out.t = h.t;
+			out.N[0] = out.N[1] = out.N[2] = 0.0;
+			if (hit) {
+				finalize_hit(sim.S, o, d, h);
+				out.obj = h.obj;
+				out.face = h.face;
+				out.N[0] = h.N.x; out.N[1] = h.N.y; out.N[2] = h.N.z;
+			}
+			hits[k] = out;
+		}
+		if (rgb) {
+			RayTask r = make_root(o, d, depth);
+			d3 c = prune ? trace_tree<true>(sim.S, *prm, r, nullptr) : trace_tree<false>(sim.S, *prm, r, nullptr);
+			rgb[3 * k] = c.x; rgb[3 * k + 1] = c.y; rgb[3 * k + 2] = c.z;
+		}
+	}
+	return 0;
+}
+
+// No-AA / supersampled frame (RayTracer::traceImage's first two branches, RayTracer.cpp:279-314)
+int sim_render(const void* arena, const rt_params* prm, int w, int h, uint8_t* rgb_out, rt_stats* stats)
+{
+	Sim sim;
+	setup(sim, arena);
+	const int s = (prm->aa_mode == RT_AA_SUPERSAMPLE || prm->aa_mode == RT_AA_JITTERED) ? prm->aa_samples : 1;
+	if (prm->aa_mode == RT_AA_ADAPTIVE) return 1;
+	std::vector<rt_stats> st(omp_get_max_threads());
+	for (auto& x : st) std::memset(&x, 0, sizeof(x));
+#pragma omp parallel for collapse(2) schedule(dynamic, 16)
+	for (int j = 0; j < h; j++)
+		for (int i = 0; i < w; i++) {
+			d3 col = mk3(0, 0, 0);
+			for (int a = 0; a < s; a++)
+				for (int b = 0; b < s; b++) {
+					const double x = double(i * s + a) / (double(w) * s), y = double(j * s + b) / (double(h) * s);
+					col = col + sample_colour<true>(sim.S, *prm, x, y, &st[omp_get_thread_num()]);
+				}
+			if (s > 1) col = mk3(col.x / double(s * s), col.y / double(s * s), col.z / double(s * s));
+			uint8_t* px = rgb_out + ((size_t)i + (size_t)j * w) * 3;
+			px[0] = (uint8_t)(int)(255.0 * col.x);
+			px[1] = (uint8_t)(int)(255.0 * col.y);
+			px[2] = (uint8_t)(int)(255.0 * col.z);
+		}
+	if (stats) {
+		std::memset(stats, 0, sizeof(*stats));
+		for (auto& x : st) {
+			stats->camera_rays += x.camera_rays;
+			stats->reflection_rays += x.reflection_rays;
+			stats->refraction_rays += x.refraction_rays;
+			stats->shadow_rays += x.shadow_rays;
+		}
+	}
+	return 0;
+}
+
+} // extern "C"

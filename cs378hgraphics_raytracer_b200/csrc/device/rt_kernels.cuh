@@ -1,0 +1,416 @@
+// rt_kernels.cuh - the sm_100a kernels of the trace loop.
+//
+// k_trace_pool is the hot kernel: RayTracer::traceImage's pixel loop and traceRay's recursion
+// (reference ray/src/RayTracer.cpp:279-314, 108-174) as a persistent-warp wavefront.  Every warp
+//   * pulls chunks of primary-ray slots (camera samples x lens positions, or caller-supplied
+//     rays) from one global atomic cursor - 32 consecutive slots are an 8x4 pixel block of a
+//     32x32 tile, so a warp's primaries are coherent;
+//   * owns a LIFO pool of pending secondary rays in HBM/L2 (SoA, one slab per warp);
+//   * each iteration refills idle lanes from the pool first (ballot + popc ranks), then from the
+//     cursor, traces + shades one ray per lane, and pushes the reflection/refraction children of
+//     all lanes back with a warp-scan compaction.
+// The recursion's return value becomes a forward weight (see RayTask), so a ray's contribution is
+// added to its camera sample's accumulator (FP64 atomics) the moment it is shaded and no parent
+// ever waits for a child.  Shadow rays are traced inline by the shading lane.
+#pragma once
+#include <cuda_runtime.h>
+#include "rt_shade.cuh"
+
+namespace rtd {
+
+enum { SRC_GRID = 0, SRC_XY = 1, SRC_RAYS = 2 };
+#define RT_TILE 32
+#define RT_TILE_PIX (RT_TILE * RT_TILE)
+#define RT_CHUNK 32
+#define RT_POOL_DOUBLES 12
+
+struct PoolArgs {
+	rt_params prm;
+	int src;
+	int w, h;           // image size (SRC_GRID)
+	int spp_side;       // supersample grid side s (1 = none)
+	int lenses;         // primary rays per sample (1, or divs+1 with depth of field)
+	int part, n_parts;  // this context renders tiles t with t % n_parts == part
+	int tiles_x, tiles_y;
+	int depth;          // traceRay depth of primaries
+	double eye_shift;   // anaglyph second eye
+	long long n_slots;  // primary-ray slots in this launch
+	const double* xs;   // SRC_XY: sample window coordinates
+	const double* ys;
+	const rt_ray* rays; // SRC_RAYS
+	double* accum;      // 3 doubles per sample
+	unsigned long long* cursor;
+	unsigned long long* stats; // camera, reflection, refraction, shadow, overflow flag
+	double* pool_d;     // per warp: RT_POOL_DOUBLES x cap doubles
+	int* pool_i;        // per warp: 2 x cap ints
+	int cap;            // pool capacity per warp (entries)
+};
+
+// local tile k of this partition -> global tile id
+__device__ __forceinline__ long long grid_samples_per_tile(const PoolArgs& A) { return (long long)RT_TILE_PIX * A.spp_side * A.spp_side; }
+
+// sample index (local to this partition) -> pixel and window coordinates; false if outside the image
+__device__ __forceinline__ bool grid_sample(const PoolArgs& A, long long sample, int& pi, int& pj, double& x, double& y)
+{
+	const int spp = A.spp_side * A.spp_side;
+	const long long pix = sample / spp;
+	const int sub = (int)(sample % spp);
+	const long long ltile = pix / RT_TILE_PIX;
+	const int p = (int)(pix % RT_TILE_PIX);
+	const long long tile = ltile * A.n_parts + A.part;
+	const int tx = (int)(tile % A.tiles_x), ty = (int)(tile / A.tiles_x);
+	const int b = p >> 5, wi = p & 31;
+	pi = tx * RT_TILE + (b & 3) * 8 + (wi & 7);
+	pj = ty * RT_TILE + (b >> 2) * 4 + (wi >> 3);
+	if (pi >= A.w || pj >= A.h) return false;
+	// RayTracer::tracePixel (RayTracer.cpp:87-88) on sub-pixel (i*s + a, j*s + b), a outer, b inner (:292-296)
+	const int s = A.spp_side;
+	const int a = sub / s, bb = sub % s;
+	x = double(pi * s + a) / (double(A.w) * s);
+	y = double(pj * s + bb) / (double(A.h) * s);
+	return true;
+}
+
+__device__ __forceinline__ void pool_store(const PoolArgs& A, double* pd, int* pi, int slot, const RayTask& t, int sample)
+{
+	const int cap = A.cap;
+	pd[0 * cap + slot] = t.o.x; pd[1 * cap + slot] = t.o.y; pd[2 * cap + slot] = t.o.z;
+	pd[3 * cap + slot] = t.d.x; pd[4 * cap + slot] = t.d.y; pd[5 * cap + slot] = t.d.z;
+	pd[6 * cap + slot] = t.weight.x; pd[7 * cap + slot] = t.weight.y; pd[8 * cap + slot] = t.weight.z;
+	pd[9 * cap + slot] = t.att_kt.x; pd[10 * cap + slot] = t.att_kt.y; pd[11 * cap + slot] = t.att_kt.z;
+	pi[0 * cap + slot] = sample;
+	pi[1 * cap + slot] = t.depth | (t.att_mode << 8) | (t.kind << 12);
+}
+__device__ __forceinline__ void pool_load(const PoolArgs& A, const double* pd, const int* pi, int slot, RayTask& t, int& sample)
+{
+	const int cap = A.cap;
+	t.o = mk3(pd[0 * cap + slot], pd[1 * cap + slot], pd[2 * cap + slot]);
+	t.d = mk3(pd[3 * cap + slot], pd[4 * cap + slot], pd[5 * cap + slot]);
+	t.weight = mk3(pd[6 * cap + slot], pd[7 * cap + slot], pd[8 * cap + slot]);
+	t.att_kt = mk3(pd[9 * cap + slot], pd[10 * cap + slot], pd[11 * cap + slot]);
+	sample = pi[0 * cap + slot];
+	const int m = pi[1 * cap + slot];
+	t.depth = m & 255;
+	t.att_mode = (m >> 8) & 15;
+	t.kind = (m >> 12) & 15;
+}
+
+#ifndef RT_POOL_THREADS
+#define RT_POOL_THREADS 128
+#endif
+
+__global__ void __launch_bounds__(RT_POOL_THREADS) k_trace_pool(const DScene S, const PoolArgs A)
+{
+	const unsigned lane = threadIdx.x & 31;
+	const unsigned lt_mask = (1u << lane) - 1u;
+	const long long warp_global = (long long)blockIdx.x * (RT_POOL_THREADS / 32) + (threadIdx.x >> 5);
+	double* pd = A.pool_d + warp_global * (long long)A.cap * RT_POOL_DOUBLES;
+	int* pi = A.pool_i + warp_global * (long long)A.cap * 2;
+
+	int count = 0;                  // entries in this warp's pool (warp-uniform)
+	long long cam_next = 0, cam_end = 0; // reserved slice of the global cursor (warp-uniform)
+	bool exhausted = false;
+	bool has_task = false;
+	RayTask task;
+	int sample = 0;
+	unsigned n_cam = 0, n_refl = 0, n_refr = 0, n_shadow = 0, overflow = 0;
+
+	for (;;) {
+		// ---- refill idle lanes: pool first, then fresh primaries --------------------------------
+		const unsigned idle_mask = __ballot_sync(0xffffffffu, !has_task);
+		int n_idle = __popc(idle_mask);
+		if (n_idle) {
+			const int rank = __popc(idle_mask & lt_mask);
+			const int take = n_idle < count ? n_idle : count;
+			if (!has_task && rank < take) {
+				pool_load(A, pd, pi, count - 1 - rank, task, sample);
+				has_task = true;
+			}
+			count -= take;
+			int need = n_idle - take;
+			int served = take;
+			while (need > 0 && !exhausted) {
+				if (cam_next >= cam_end) {
+					unsigned long long base = 0;
+					if (lane == 0) base = atomicAdd(A.cursor, (unsigned long long)RT_CHUNK);
+					base = __shfl_sync(0xffffffffu, base, 0);
+					if ((long long)base >= A.n_slots) { exhausted = true; break; }
+					cam_next = (long long)base;
+					cam_end = cam_next + RT_CHUNK < A.n_slots ? cam_next + RT_CHUNK : A.n_slots;
+				}
+				const int avail = (int)(cam_end - cam_next);
+				const int give = need < avail ? need : avail;
+				if (!has_task && rank >= served && rank < served + give) {
+					const long long slot = cam_next + (rank - served);
+					const long long smp = slot / A.lenses;
+					const int lens = (int)(slot % A.lenses);
+					bool ok = true;
+					if (A.src == SRC_RAYS) {
+						task.o = ld3(A.rays[slot].p);
+						task.d = ld3(A.rays[slot].d);
+					} else {
+						double x, y;
+						if (A.src == SRC_GRID) {
+							int pi_, pj_;
+							ok = grid_sample(A, smp, pi_, pj_, x, y);
+						} else {
+							x = A.xs[smp];
+							y = A.ys[smp];
+						}
+						if (ok) primary_ray(S.cam, A.prm, x, y, lens, A.eye_shift, task.o, task.d);
+					}
+					if (ok) {
+						task.weight = mk3(1.0, 1.0, 1.0);
+						task.att_kt = mk3(1.0, 1.0, 1.0);
+						task.att_mode = 0;
+						task.depth = A.depth;
+						task.kind = 0;
+						sample = (int)smp;
+						has_task = true;
+					}
+				}
+				cam_next += give;
+				served += give;
+				need -= give;
+			}
+		}
+		if (!__any_sync(0xffffffffu, has_task)) {
+			if (exhausted && count == 0) break;
+			continue;
+		}
+		// ---- trace + shade one ray per lane -----------------------------------------------------
+		RayTask kids[2];
+		int n_kids = 0;
+		if (has_task) {
+			Hit h;
+			unsigned sh = 0;
+			const d3 c = trace_step<true>(S, A.prm, task, h, kids, n_kids, sh);
+			n_shadow += sh;
+			if (task.kind == 0) n_cam++;
+			else if (task.kind == 1) n_refl++;
+			else n_refr++;
+			double* acc = A.accum + 3ll * sample;
+			if (c.x != 0.0) atomicAdd(acc + 0, c.x);
+			if (c.y != 0.0) atomicAdd(acc + 1, c.y);
+			if (c.z != 0.0) atomicAdd(acc + 2, c.z);
+		}
+		// ---- push children: warp-scan compaction into the pool ----------------------------------
+		int incl = n_kids;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const int v = __shfl_up_sync(0xffffffffu, incl, o);
+			if ((int)lane >= o) incl += v;
+		}
+		const int total = __shfl_sync(0xffffffffu, incl, 31);
+		if (total) {
+			if (count + total > A.cap) {
+				overflow = 1; // never expected (cap = 32*(depth+3)); reported through stats[4]
+			} else {
+				const int base = count + incl - n_kids;
+				for (int k = 0; k < n_kids; k++) pool_store(A, pd, pi, base + k, kids[k], sample);
+				count += total;
+			}
+		}
+		has_task = false;
+	}
+	// ---- ray counters ------------------------------------------------------------------------------
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		n_cam += __shfl_down_sync(0xffffffffu, n_cam, o);
+		n_refl += __shfl_down_sync(0xffffffffu, n_refl, o);
+		n_refr += __shfl_down_sync(0xffffffffu, n_refr, o);
+		n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
+		overflow |= __shfl_down_sync(0xffffffffu, overflow, o);
+	}
+	if (lane == 0) {
+		if (n_cam) atomicAdd(A.stats + 0, (unsigned long long)n_cam);
+		if (n_refl) atomicAdd(A.stats + 1, (unsigned long long)n_refl);
+		if (n_refr) atomicAdd(A.stats + 2, (unsigned long long)n_refr);
+		if (n_shadow) atomicAdd(A.stats + 3, (unsigned long long)n_shadow);
+		if (overflow) atomicAdd(A.stats + 4, 1ull);
+	}
+}
+
+// ---- Scene::intersect for caller-supplied rays (rt_trace_rays hits) ---------------------------
+__global__ void __launch_bounds__(128) k_hits(const DScene S, const rt_ray* rays, int n, rt_hit* out)
+{
+	const int k = blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	const d3 o = ld3(rays[k].p), d = ld3(rays[k].d);
+	Hit h;
+	rt_hit r;
+	r.obj = r.face = -1;
+	r.N[0] = r.N[1] = r.N[2] = 0.0;
+	if (closest_hit<true>(S, o, d, h)) {
+		finalize_hit(S, o, d, h);
+		r.obj = h.obj;
+		r.face = h.face;
+		r.N[0] = h.N.x; r.N[1] = h.N.y; r.N[2] = h.N.z;
+	}
+	r.t = h.t;
+	out[k] = r;
+}
+
+// RayTracer::trace's tail for one sample (RayTracer.cpp:74-78): mean over the lens rays, clamp
+__device__ __forceinline__ d3 sample_value(const double* accum, long long sample, const rt_params& prm)
+{
+	d3 c = mk3(accum[3 * sample], accum[3 * sample + 1], accum[3 * sample + 2]);
+	if (prm.dof_on) c = c * (1.0 / (prm.dof_divs + 1.0));
+	return gclamp(c, 0.0, 1.0);
+}
+
+// RayTracer::setPixel (RayTracer.cpp:388-394)
+__device__ __forceinline__ void store_pixel(uint8_t* fb, int w, int i, int j, d3 c)
+{
+	uint8_t* px = fb + ((size_t)i + (size_t)j * w) * 3;
+	px[0] = (uint8_t)(int)(255.0 * c.x);
+	px[1] = (uint8_t)(int)(255.0 * c.y);
+	px[2] = (uint8_t)(int)(255.0 * c.z);
+}
+
+// No-AA and supersampled resolve (RayTracer.cpp:288-298, 310): one thread per local pixel.
+// accum2 (optional) holds the anaglyph second-eye samples whose red channel replaces the first's.
+__global__ void __launch_bounds__(256) k_resolve_grid(const PoolArgs A, const double* accum2, long long n_pix, uint8_t* fb)
+{
+	const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (pix >= n_pix) return;
+	const int spp = A.spp_side * A.spp_side;
+	int pi, pj;
+	double x, y;
+	if (!grid_sample(A, pix * spp, pi, pj, x, y)) return;
+	d3 col = mk3(0.0, 0.0, 0.0);
+	for (int s = 0; s < spp; s++) {
+		d3 c = sample_value(A.accum, pix * spp + s, A.prm);
+		if (accum2) c.x = sample_value(accum2, pix * spp + s, A.prm).x;
+		col = col + c;
+	}
+	if (spp > 1) {
+		const double dv = double(spp);
+		col = mk3(col.x / dv, col.y / dv, col.z / dv);
+	}
+	store_pixel(fb, A.w, pi, pj, col);
+}
+
+// ---- adaptive anti-aliasing (RayTracer::adaptaa, RayTracer.cpp:316-365) -------------------------
+// A region is one adaptaa call: window [x1,x2]x[y1,y2] of pixel `pix` at recursion level `level`.
+struct Region {
+	double x1, x2, y1, y2;
+	int pix;   // local pixel index
+	int level;
+};
+
+// hammersley(k, N) (reference util.cpp:3-11): radical inverse base 2; the second coordinate is
+// always 0 because n has been shifted down to 0 by the time it is used.
+__device__ __forceinline__ double radical_inverse2(int n)
+{
+	double mul = 0.5, result = 0.0;
+	while (n > 0) {
+		result += (n % 2) ? mul : 0;
+		n /= 2;
+		mul /= 2.0;
+	}
+	return result;
+}
+
+__global__ void __launch_bounds__(256) k_adapt_init(const PoolArgs A, long long n_pix, Region* regions)
+{
+	const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (pix >= n_pix) return;
+	int pi, pj;
+	double x, y;
+	Region r;
+	r.pix = (int)pix;
+	r.level = 0;
+	if (grid_sample(A, pix, pi, pj, x, y)) {
+		r.x1 = double(pi) / double(A.w);
+		r.x2 = double(pi + 1) / double(A.w);
+		r.y1 = double(pj) / double(A.h);
+		r.y2 = double(pj + 1) / double(A.h);
+	} else {
+		r.x1 = r.x2 = r.y1 = r.y2 = 0.0; // outside the image: fails the size test, contributes nothing
+	}
+	regions[pix] = r;
+}
+
+// sample coordinates of every region of one level
+__global__ void __launch_bounds__(256) k_adapt_samples(const Region* regions, long long n_regions, int N, double* xs, double* ys)
+{
+	const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n_regions * N) return;
+	const Region r = regions[t / N];
+	const int k = (int)(t % N);
+	const double w = r.x2 - r.x1, h = r.y2 - r.y1;
+	xs[t] = radical_inverse2(k) * w + r.x1;
+	ys[t] = 0.0 * h + r.y1;
+}
+
+// mean / deviation test of each region; either adds its mean (scaled by 4^-level) to the pixel or
+// emits its four quadrants for the next level.  valid(region) is adaptaa's first line (:319).
+__device__ __forceinline__ bool region_valid(const Region& r) { return !(r.x1 + 0.0001 >= r.x2 || r.y1 + 0.0001 >= r.y2); }
+
+__global__ void __launch_bounds__(256) k_adapt_resolve(const Region* regions, long long n_regions, int N, const double* accum, rt_params prm,
+                                                      double* pix_accum, Region* next, unsigned long long* next_count, unsigned long long next_cap)
+{
+	const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n_regions) return;
+	const Region r = regions[t];
+	if (!region_valid(r)) return; // val left at its zero initialisation
+	d3 mu = mk3(0.0, 0.0, 0.0);
+	for (int k = 0; k < N; k++) mu = mu + sample_value(accum, t * N + k, prm);
+	mu = mu * (1.0 / N);
+	d3 sd = mk3(0.0, 0.0, 0.0);
+	for (int k = 0; k < N; k++) {
+		const d3 c = sample_value(accum, t * N + k, prm);
+		const d3 a = mk3(fabs(c.x - mu.x), fabs(c.y - mu.y), fabs(c.z - mu.z));
+		sd = sd + a * a; // pow(|s - mu|, 2.0) is the correctly rounded square
+	}
+	sd = sd * (1.0 / (N - 1));
+	double scale = 1.0;
+	for (int l = 0; l < r.level; l++) scale *= 0.25;
+	if (length(sd) > prm.aa_thresh) {
+		const double xs[3] = {r.x1, (r.x1 + r.x2) / 2.0, r.x2};
+		const double ys[3] = {r.y1, (r.y1 + r.y2) / 2.0, r.y2};
+		for (int i = 0; i < 2; i++)
+			for (int j = 0; j < 2; j++) {
+				Region c;
+				c.x1 = xs[i]; c.x2 = xs[i + 1]; c.y1 = ys[j]; c.y2 = ys[j + 1];
+				c.pix = r.pix;
+				c.level = r.level + 1;
+				if (!region_valid(c)) continue; // returns with val = 0
+				const unsigned long long at = atomicAdd(next_count, 1ull);
+				if (at < next_cap) next[at] = c;
+			}
+		return;
+	}
+	mu = mu * scale;
+	atomicAdd(pix_accum + 3ll * r.pix + 0, mu.x);
+	atomicAdd(pix_accum + 3ll * r.pix + 1, mu.y);
+	atomicAdd(pix_accum + 3ll * r.pix + 2, mu.z);
+}
+
+__global__ void __launch_bounds__(256) k_adapt_store(const PoolArgs A, long long n_pix, const double* pix_accum, uint8_t* fb)
+{
+	const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (pix >= n_pix) return;
+	int pi, pj;
+	double x, y;
+	if (!grid_sample(A, pix, pi, pj, x, y)) return;
+	store_pixel(fb, A.w, pi, pj, mk3(pix_accum[3 * pix], pix_accum[3 * pix + 1], pix_accum[3 * pix + 2]));
+}
+
+} // namespace rtd
+
+namespace rtd {
+// RayTracer::tracePixel's return value for explicit samples (clamped mean over lens rays,
+// anaglyph red from the second eye)
+__global__ void __launch_bounds__(256) k_sample_values(const double* accum, const double* accum2, long long n, rt_params prm, double* out)
+{
+	const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	d3 c = sample_value(accum, k, prm);
+	if (accum2) c.x = sample_value(accum2, k, prm).x;
+	out[3 * k] = c.x;
+	out[3 * k + 1] = c.y;
+	out[3 * k + 2] = c.z;
+}
+} // namespace rtd

@@ -79,8 +79,17 @@ std::unordered_map<const void*, std::pair<int, int>> g_ids; // SceneObject* -> (
 struct alignas(64) Counters {
 	uint64_t camera, reflection, refraction, shadow;
 };
-Counters g_cnt[256];
+Counters g_cnt[1024];
 bool g_counting = true;
+// one slot per OS thread (omp_get_thread_num() is 0 for every thread inside the reference's nested,
+// serialised parallel regions of adaptaa, RayTracer.cpp:330-337, so it cannot be the index)
+std::atomic<int> g_next_slot{0};
+thread_local int t_slot = -1;
+inline Counters& my_counters()
+{
+	if (t_slot < 0) t_slot = g_next_slot.fetch_add(1) & 1023;
+	return g_cnt[t_slot];
+}
 
 void reset_counters() { std::memset(g_cnt, 0, sizeof(g_cnt)); }
 
@@ -170,7 +179,7 @@ std::vector<isect> wrap_Scene_intersectList(const Scene*, ray&) asm("__wrap__ZNK
 bool wrap_Scene_intersect(const Scene* s, ray& r, isect& i)
 {
 	if (g_counting) {
-		Counters& c = g_cnt[omp_get_thread_num() & 255];
+		Counters& c = my_counters();
 		switch (r.type()) {
 		case ray::REFLECTION: c.reflection++; break;
 		case ray::REFRACTION: c.refraction++; break;
@@ -181,7 +190,7 @@ bool wrap_Scene_intersect(const Scene* s, ray& r, isect& i)
 }
 std::vector<isect> wrap_Scene_intersectList(const Scene* s, ray& r)
 {
-	if (g_counting) g_cnt[omp_get_thread_num() & 255].shadow++;
+	if (g_counting) my_counters().shadow++;
 	return real_Scene_intersectList(s, r);
 }
 
@@ -477,7 +486,7 @@ int ref_render(int w, int h, uint8_t* rgb_out, double* seconds_out, rt_stats* st
 	if (rgb_out && buf) std::memcpy(rgb_out, buf, (size_t)w * h * 3);
 	if (stats_out) {
 		std::memset(stats_out, 0, sizeof(*stats_out));
-		for (int t = 0; t < 256; t++) {
+		for (int t = 0; t < 1024; t++) {
 			stats_out->camera_rays += g_cnt[t].camera;
 			stats_out->reflection_rays += g_cnt[t].reflection;
 			stats_out->refraction_rays += g_cnt[t].refraction;
@@ -527,7 +536,7 @@ int ref_render_window(int w, int h, int i0, int i1, int j0, int j1, uint8_t* rgb
 	(void)wh;
 	if (stats_out) {
 		std::memset(stats_out, 0, sizeof(*stats_out));
-		for (int t = 0; t < 256; t++) {
+		for (int t = 0; t < 1024; t++) {
 			stats_out->camera_rays += g_cnt[t].camera;
 			stats_out->reflection_rays += g_cnt[t].reflection;
 			stats_out->refraction_rays += g_cnt[t].refraction;

@@ -1,0 +1,201 @@
+"""GPU parity tests proper: the CUDA path, called through the C-ABI (librt_b200.so), against the
+oracle (the unmodified reference built into oracle/_ref/libref_oracle.so) on the same scenes.
+
+Bars (BASELINE.json north_star):
+  * hit primitive ids of primary rays: bit-exact (we also require t and N bit-exact)
+  * frames: max-channel |delta| <= 1/255 on >= 99.9 % of pixels
+  * ray counters: equal up to the pixel mismatch rate
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SCENES = ["hitchcock.ray", "trimesh2.ray", "dragon_small.ray", "mixed_small.ray", "prims_mixed.ray"]
+W = 320
+TOL_WITHIN1 = 0.999
+
+
+@pytest.fixture(scope="module")
+def ctx(rtlib):
+    c = rtlib.Context(0)
+    yield c
+    c.close()
+
+
+def _load(rtlib, oracle_mod, ctx, path, cubemap=None):
+    arena = rtlib.load_ray_file(str(path), cubemap)
+    ctx.upload(arena)
+    orc = oracle_mod.Oracle(str(path), cubemap)
+    return arena, orc
+
+
+@pytest.mark.parametrize("scene", SCENES)
+def test_primary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_dir, scene):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+    h = oracle_mod.frame_height(W, orc.aspect)
+    rays = oracle_mod.camera_rays(arena.camera(), W, h)
+    p = rtlib.Params.default(depth=5)
+    ref_hits, _ = orc.trace_rays(p, rays, 5, want_rgb=False)
+    dev_hits, _ = ctx.trace_rays(p, rays, 5, want_rgb=False)
+    assert (ref_hits["obj"] >= 0).sum() > 100, "scene not in view"
+    assert np.array_equal(ref_hits["obj"], dev_hits["obj"])
+    assert np.array_equal(ref_hits["face"], dev_hits["face"])
+    assert np.array_equal(ref_hits["t"], dev_hits["t"])
+    assert np.array_equal(ref_hits["N"], dev_hits["N"])
+
+
+@pytest.mark.parametrize("scene", SCENES)
+def test_secondary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_dir, scene):
+    """Rays that start ON surfaces (the self-intersection epsilons): reflect every primary hit."""
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+    h = oracle_mod.frame_height(160, orc.aspect)
+    rays = oracle_mod.camera_rays(arena.camera(), 160, h)
+    p = rtlib.Params.default(depth=5)
+    hits, _ = orc.trace_rays(p, rays, 5, want_rgb=False)
+    m = hits["obj"] >= 0
+    o, d, t, n = rays[m, 0:3], rays[m, 3:6], hits["t"][m], hits["N"][m]
+    c = -(n * d).sum(axis=1)
+    sec = np.zeros((m.sum(), 6))
+    sec[:, 0:3] = o + (t - 1e-8)[:, None] * d
+    sec[:, 3:6] = d + (2 * c)[:, None] * n
+    ref_hits, _ = orc.trace_rays(p, sec, 5, want_rgb=False)
+    dev_hits, _ = ctx.trace_rays(p, sec, 5, want_rgb=False)
+    for f in ("obj", "face", "t", "N"):
+        assert np.array_equal(ref_hits[f], dev_hits[f]), f
+
+
+@pytest.mark.parametrize("scene", SCENES)
+def test_trace_ray_colours(rtlib, oracle_mod, ctx, scene_dir, scene):
+    """RayTracer::traceRay colours (unclamped doubles): only libm pow/sin/cos and the summation
+    order differ between host and device, so 1e-9 absolute is generous."""
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+    h = oracle_mod.frame_height(128, orc.aspect)
+    rays = oracle_mod.camera_rays(arena.camera(), 128, h)
+    p = rtlib.Params.default(depth=5)
+    _, ref_rgb = orc.trace_rays(p, rays, 5, want_hits=False)
+    _, dev_rgb = ctx.trace_rays(p, rays, 5, want_hits=False)
+    assert np.abs(ref_rgb - dev_rgb).max() < 1e-9
+
+
+@pytest.mark.parametrize("scene", SCENES)
+def test_frame_and_ray_counts(rtlib, oracle_mod, ctx, scene_dir, scene):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+    h = oracle_mod.frame_height(W, orc.aspect)
+    p = rtlib.Params.default(depth=5)
+    ref_img, ref_st, _ = orc.render(p, W, h)
+    dev_img, dev_st = ctx.render(p, W, h)
+    d = oracle_mod.image_diff(ref_img, dev_img)
+    assert d["within1"] >= TOL_WITHIN1, d
+    assert d["rms"] < 10.0, d  # raycheck.py's own pass criterion
+    assert dev_st.camera_rays == ref_st.camera_rays == W * h
+    for f in ("reflection_rays", "refraction_rays", "shadow_rays"):
+        a, b = getattr(ref_st, f), getattr(dev_st, f)
+        assert abs(a - b) <= max(2, 1e-3 * max(a, b)), (f, a, b)
+    assert dev_st.launches >= 2
+
+
+def test_depth_zero_and_one(rtlib, oracle_mod, ctx, scene_dir):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "hitchcock.ray")
+    for depth in (0, 1, 2):
+        p = rtlib.Params.default(depth=depth)
+        ref_img, ref_st, _ = orc.render(p, 200, 200)
+        dev_img, dev_st = ctx.render(p, 200, 200)
+        assert oracle_mod.image_diff(ref_img, dev_img)["within1"] >= TOL_WITHIN1
+        assert ref_st.reflection_rays == dev_st.reflection_rays
+        if depth < 2:
+            assert dev_st.reflection_rays == 0 and dev_st.refraction_rays == 0
+
+
+def test_supersampling(rtlib, oracle_mod, ctx, scene_dir):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "hitchcock.ray")
+    p = rtlib.Params.default(depth=5, aa_mode=1, aa_samples=3)
+    ref_img, ref_st, _ = orc.render(p, 160, 160)
+    dev_img, dev_st = ctx.render(p, 160, 160)
+    assert oracle_mod.image_diff(ref_img, dev_img)["within1"] >= TOL_WITHIN1
+    assert dev_st.camera_rays == ref_st.camera_rays == 160 * 160 * 9
+
+
+def test_depth_of_field(rtlib, oracle_mod, ctx, scene_dir):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "trimesh2.ray")
+    p = rtlib.Params.default(depth=5, dof_on=1, dof_fd=2.5, dof_divs=5, dof_apsz=0.05)
+    ref_img, ref_st, _ = orc.render(p, 200, 200)
+    dev_img, dev_st = ctx.render(p, 200, 200)
+    assert oracle_mod.image_diff(ref_img, dev_img)["within1"] >= TOL_WITHIN1
+    assert dev_st.camera_rays == ref_st.camera_rays == 200 * 200 * 6
+
+
+def test_adaptive_aa_with_cubemap(rtlib, oracle_mod, ctx, scene_dir, cubemap_faces):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "hitchcock.ray", cubemap_faces)
+    for thresh in (1.0, 0.01):
+        p = rtlib.Params.default(depth=5, aa_mode=2, aa_samples=3, aa_thresh=thresh, use_cubemap=1)
+        ref_img, ref_st, _ = orc.render(p, 128, 128)
+        dev_img, dev_st = ctx.render(p, 128, 128)
+        d = oracle_mod.image_diff(ref_img, dev_img)
+        assert d["within1"] >= 0.995, d  # the subdivision decision itself is a float threshold
+        assert abs(int(dev_st.camera_rays) - int(ref_st.camera_rays)) <= 0.02 * ref_st.camera_rays
+
+
+def test_cubemap_and_supersample(rtlib, oracle_mod, ctx, scene_dir, cubemap_faces):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "hitchcock.ray", cubemap_faces)
+    p = rtlib.Params.default(depth=5, aa_mode=1, aa_samples=2, use_cubemap=1)
+    ref_img, _, _ = orc.render(p, 160, 160)
+    dev_img, _ = ctx.render(p, 160, 160)
+    assert oracle_mod.image_diff(ref_img, dev_img)["within1"] >= TOL_WITHIN1
+    assert ref_img[0, 0].sum() > 0  # the background is the cube map, not black
+
+
+def test_anaglyph_and_adaptive_termination(rtlib, oracle_mod, ctx, scene_dir):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "prims_mixed.ray")
+    h = oracle_mod.frame_height(200, orc.aspect)
+    for kw in (dict(anaglyph=1), dict(aterm_thresh=0.05)):
+        p = rtlib.Params.default(depth=5, **kw)
+        ref_img, _, _ = orc.render(p, 200, h)
+        dev_img, _ = ctx.render(p, 200, h)
+        assert oracle_mod.image_diff(ref_img, dev_img)["within1"] >= TOL_WITHIN1, kw
+
+
+def test_trace_pixels(rtlib, oracle_mod, ctx, scene_dir):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "hitchcock.ray")
+    rng = np.random.default_rng(7)
+    ij = rng.integers(0, 300, size=(500, 2)).astype(np.int32)
+    p = rtlib.Params.default(depth=5)
+    ref = orc.trace_pixels(p, 300, 300, ij)
+    dev = ctx.trace_pixels(p, 300, 300, ij)
+    assert np.abs(ref - dev).max() < 1e-9
+
+
+def test_tile_partition_is_exact(rtlib, ctx, scene_dir):
+    """Interleaved 32x32 tiles over n partitions reassemble to the single-partition frame bit for bit."""
+    arena = rtlib.load_ray_file(str(scene_dir / "hitchcock.ray"))
+    ctx.upload(arena)
+    p = rtlib.Params.default(depth=3)
+    w, h = 200, 150  # not multiples of the tile size
+    full, st_full = ctx.render(p, w, h)
+    for n in (2, 3, 8):
+        out = np.zeros((h, w, 3), np.uint8)
+        rays = 0
+        for part in range(n):
+            _, st = ctx.render(p, w, h, part, n, out=out)
+            rays += st.rays
+        assert np.array_equal(out, full)
+        assert rays == st_full.rays
+
+
+def test_empty_and_error_paths(rtlib, ctx, scene_dir):
+    arena = rtlib.load_ray_file(str(scene_dir / "hitchcock.ray"))
+    ctx.upload(arena)
+    p = rtlib.Params.default(depth=1)
+    hits, rgb = ctx.trace_rays(p, np.zeros((0, 6)), 1)
+    assert len(hits) == 0 and len(rgb) == 0
+    # a ray that misses everything: reference sets t = 1000 (scene.cpp:174-175)
+    hits, rgb = ctx.trace_rays(p, np.array([[0, 0, 100, 0, 0, 1.0]]), 1)
+    assert hits["obj"][0] == -1 and hits["t"][0] == 1000.0 and (rgb == 0).all()
+    with pytest.raises(rtlib.RtError):
+        ctx.render(rtlib.Params.default(depth=-1), 64, 64)
+    with pytest.raises(rtlib.RtError):
+        ctx.render(rtlib.Params.default(overlapping_objects=1), 64, 64)
+    fresh = rtlib.Context(0)
+    with pytest.raises(rtlib.RtError):
+        fresh.render(p, 64, 64)  # no scene
+    fresh.close()

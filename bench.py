@@ -1,0 +1,351 @@
+#!/usr/bin/env python3
+"""bench.py - throughput of the trace loop (RayTracer::traceImage) in Mrays/s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3] [--impl b200|reference]
+  (N > 1: launched by torchrun, one rank per GPU; see the contract in the task description)
+
+A step = one full frame of the workload.  rays = camera (incl. AA samples and DOF lens rays) +
+reflection + refraction + shadow rays, counted on the device exactly as the instrumented reference
+counts them.  `value` is measured with the scene resident in HBM and the frame left
+in HBM; `e2e` goes through the host-facing calls every step: rt_upload_scene (host -> device copy of
+the whole flattened scene) + render + device -> host copy of the RGB8 frame.
+
+--impl reference times the UNMODIFIED reference (oracle/_ref/libref_oracle.so) on the host cores on
+a bounded sample of the same frame.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "scenes"))
+
+# BASELINE.json configs.  All scenes are procedural stand-ins (the reference's assets are not in
+# its repository); generators and seeds in scenes/gen_scenes.py.
+WORKLOADS = {
+    "c1": dict(name="C1 hitchcock stand-in 512x512, depth 5, no AA", gen=("hitchcock", 1.0), w=512, params=dict(depth=5)),
+    "c2": dict(name="C2 trimesh2 stand-in 1024x1024, depth 5, DOF aperture 0.05 focal 2.5 divs 5", gen=("trimesh2", 1.0), w=1024,
+               params=dict(depth=5, dof_on=1, dof_fd=2.5, dof_divs=5, dof_apsz=0.05)),
+    "c3": dict(name="C3 dragon stand-in (869,556 faces, kd-tree) 1920x1080, depth 5, shadows", gen=("dragon", 1.0), w=1920,
+               params=dict(depth=5)),
+    "c4": dict(name="C4 hitchcock stand-in 2048x2048, 4x4 supersampling, cubemap, depth 5", gen=("hitchcock", 1.0), w=2048,
+               params=dict(depth=5, aa_mode=1, aa_samples=4, use_cubemap=1), cubemap=512),
+    "c4a": dict(name="C4 hitchcock stand-in 2048x2048, adaptive AA 4x4 thresh 0.01, cubemap, depth 5", gen=("hitchcock", 1.0), w=2048,
+                params=dict(depth=5, aa_mode=2, aa_samples=4, aa_thresh=0.01, use_cubemap=1), cubemap=512),
+    "c5": dict(name="C5 synthetic 1M-primitive mixed scene 7680x4320, depth 8", gen=("mixed", 1.0), w=7680, params=dict(depth=8)),
+}
+SCENE_CACHE = os.environ.get("RT_SCENE_CACHE", os.path.join(tempfile.gettempdir(), "rt_b200_scenes"))
+
+
+def scene_files(wl):
+    """Generates (once per box) the stand-in .ray text and cube map for a workload."""
+    import gen_scenes
+    os.makedirs(SCENE_CACHE, exist_ok=True)
+    gen, scale = wl["gen"]
+    path = os.path.join(SCENE_CACHE, "%s_%g.ray" % (gen, scale))
+    if not os.path.exists(path):
+        tmp = path + ".tmp%d" % os.getpid()
+        with open(tmp, "w") as f:
+            f.write(gen_scenes.GENERATORS[gen](scale))
+        os.replace(tmp, path)
+    faces = None
+    if wl.get("cubemap"):
+        d = os.path.join(SCENE_CACHE, "cubemap%d" % wl["cubemap"])
+        if not os.path.exists(os.path.join(d, "nz.bmp")):
+            gen_scenes.gen_cubemap(d, wl["cubemap"])
+        faces = [os.path.join(d, n + ".bmp") for n in ("px", "nx", "py", "ny", "pz", "nz")]
+    return path, faces
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                pass
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 8:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- the reference on the host cores ------------------------------------------------------------
+def reference_sample(orc, params, w, h, budget_s, block=128):
+    """Times the unmodified reference's per-pixel code on blocks of the workload's frame, visited
+    in a fixed scattered order, until `budget_s` seconds of traceImage-equivalent time are spent
+    (or the frame is complete).  Returns (rays, seconds, description)."""
+    bx, by = (w + block - 1) // block, (h + block - 1) // block
+    order = np.random.default_rng(12345).permutation(bx * by)
+    rays, secs, done_px = 0, 0.0, 0
+    n_blocks = 0
+    for b in order:
+        i0, j0 = (b % bx) * block, (b // bx) * block
+        i1, j1 = min(i0 + block, w), min(j0 + block, h)
+        _, st, s = orc.render_window(params, w, h, i0, i1, j0, j1)
+        rays += st.rays
+        secs += s
+        done_px += (i1 - i0) * (j1 - j0)
+        n_blocks += 1
+        if secs >= budget_s:
+            break
+    desc = "%d scattered %dx%d-pixel blocks = %.1f%% of the %dx%d frame" % (n_blocks, block, block, 100.0 * done_px / (w * h), w, h)
+    return rays, secs, desc
+
+
+def run_reference(args, wl, rank):
+    """--impl reference: rank 0 alone runs; one step = one bounded sample of the frame."""
+    if rank != 0:
+        return
+    import cs378hgraphics_raytracer_b200 as rt
+    import oracle_binding as ob
+    if not ob.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref_oracle.so missing (reference is built from /root/reference by oracle/Makefile)"}))
+        return
+    path, faces = scene_files(wl)
+    arena = rt.load_ray_file(path, faces)  # the product's loader only parses; the reference's own load of the dragon takes ~32 min
+    orc = ob.Oracle(None, arena=arena)
+    params = rt.Params.default(**wl["params"])
+    w = wl["w"]
+    h = ob.frame_height(w, orc.aspect)
+    cores = ob.ref().ref_get_threads()
+    budget = max(2.0, min(20.0, 150.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        reference_sample(orc, params, w, h, budget / 4)
+    t_rays, t_secs, desc = 0, 0.0, ""
+    for _ in range(args.steps):
+        r, s, desc = reference_sample(orc, params, w, h, budget)
+        t_rays += r
+        t_secs += s
+    value = t_rays / t_secs / 1e6
+    out = {"metric": "Mrays/s (primary+secondary+shadow)", "value": value, "unit": "Mrays/s", "impl": "reference", "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_secs / args.steps, "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": wl["name"], "width": w, "height": h, "scene": "procedural stand-in (scenes/gen_scenes.py)"},
+           "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": desc + " per step"},
+           "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+
+
+# ---- the B200 arm --------------------------------------------------------------------------------
+def load_cost_model(key):
+    """Algorithmic bytes / flops per ray of a workload (SURVEY.md 8d cost model), computed once by
+    scenes/cost_model.py with the instrumented host-sim and stored next to the scenes."""
+    p = os.path.join(ROOT, "scenes", "cost_model.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(key)
+    return None
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f).get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_b200(args, key, wl, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import cs378hgraphics_raytracer_b200 as rt
+    from cs378hgraphics_raytracer_b200 import parallel as par
+    import oracle_binding as ob
+
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    ctx = rt.Context(local_rank)
+    params = rt.Params.default(**wl["params"])
+
+    # scene: rank 0 parses + flattens, NCCL broadcast replicates it (north star: scene replicated)
+    arena_bytes = b""
+    if rank == 0:
+        path, faces = scene_files(wl)
+        a = rt.load_ray_file(path, faces)
+        arena_bytes = a.bytes()
+        a.free()
+    arena_bytes = par.broadcast_arena(arena_bytes, rank, world, device)
+    par.upload_bytes(ctx, arena_bytes)
+    hdr = np.frombuffer(arena_bytes[:32 + 17 * 24], dtype=np.uint64)
+    cam = np.frombuffer(arena_bytes[int(hdr[4 + 3 * 1 + 1]):int(hdr[4 + 3 * 1 + 1]) + 14 * 8], dtype=np.float64)
+    cam_aspect = float(cam[12])
+    w = wl["w"]
+    h = ob.frame_height(w, cam_aspect)
+    n_items = int(hdr[4 + 3 * 12 + 2])
+    h2d_bytes = len(arena_bytes) + 96 * n_items
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        ptr, st = ctx.render_device(params, w, h, rank, world)
+        full = None
+        if world > 1:
+            full = par.gather_frame(par.device_frame(ptr, w, h, device), rank, world)
+            torch.cuda.synchronize()
+        return st, full
+
+    def step_e2e(host_out):
+        par.upload_bytes(ctx, arena_bytes)
+        if world == 1:
+            _, st = ctx.render(params, w, h, out=host_out)
+        else:
+            ptr, st = ctx.render_device(params, w, h, rank, world)
+            full = par.gather_frame(par.device_frame(ptr, w, h, device), rank, world)
+            if rank == 0:
+                host_out[...] = full.cpu().numpy()
+            torch.cuda.synchronize()
+        return st
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    rays = launches = 0
+    dev_ms = 0.0
+    for _ in range(args.steps):
+        st, _ = step_resident()
+        rays += st.rays
+        launches += st.launches
+        dev_ms += st.device_ms
+    barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop() if rank == 0 else None
+    # the L2 flush is not part of the step: measure it alone and take it out
+    torch.cuda.synchronize()
+    f0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+    flush_s = time.perf_counter() - f0
+    elapsed = max(1e-9, (t1 - t0) - flush_s)
+
+    host_out = np.zeros((h, w, 3), np.uint8)
+    step_e2e(host_out)
+    barrier()
+    e0 = time.perf_counter()
+    e_rays = 0
+    for _ in range(args.steps):
+        e_rays += step_e2e(host_out).rays
+    barrier()
+    e1 = time.perf_counter()
+
+    stats = torch.tensor([float(rays), float(e_rays), float(launches), elapsed, e1 - e0, dev_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        sums = stats.clone()
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+        maxs = stats.clone()
+        dist.all_reduce(maxs, op=dist.ReduceOp.MAX)
+    else:
+        sums = maxs = stats
+    if rank == 0:
+        tot_rays, tot_e_rays, tot_launches = float(sums[0]), float(sums[1]), int(sums[2])
+        t_max, e_max, dev_ms_max = float(maxs[3]), float(maxs[4]), float(maxs[5])
+        value = tot_rays / t_max / 1e6
+        out = {"metric": "Mrays/s (primary+secondary+shadow)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+               "warmup": args.warmup, "ms_per_step": 1e3 * t_max / args.steps, "higher_is_better": True, "scaling": "strong",
+               "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+               "config": {"workload": wl["name"], "width": w, "height": h, "rays_per_frame": tot_rays / args.steps,
+                          "scene": "procedural stand-in (scenes/gen_scenes.py); real asset not in the reference repo",
+                          "partition": "interleaved 32x32 tiles, tile t -> rank t %% %d; scene replicated" % world,
+                          "l2": "256 MiB L2 flush between timed frames (its own time subtracted)"},
+               "clocks": clocks, "gpu_launches": tot_launches,
+               "e2e": {"value": tot_e_rays / e_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": w * h * 3,
+                       "what": "rt_upload_scene (whole scene host->device) + render + RGB8 frame device->host, every step"}}
+        # roofline of the dominant kernel (k_trace_pool): algorithmic bytes per ray x rays / kernel time
+        cm = load_cost_model(key)
+        peak, peak_src = measured_peaks()
+        if cm:
+            alg_bytes = cm["bytes_per_ray"] * (tot_rays / args.steps / world)
+            k_ms = dev_ms_max / args.steps
+            ach = alg_bytes / (k_ms * 1e-3) / 1e9
+            out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": cm.get("dram_traffic_bytes"),
+                               "peak_source": peak_src, "kernel": "k_trace_pool", "kernel_ms": k_ms, "bytes_per_ray": cm["bytes_per_ray"],
+                               "fp64": {"flops_per_ray": cm.get("flops_per_ray"),
+                                        "achieved_tflops": (cm.get("flops_per_ray", 0) * tot_rays / args.steps / world) / (k_ms * 1e-3) / 1e12}}
+        else:
+            out["roofline"] = None
+        # the reference on this box's host cores, bounded sample (N = 1 only)
+        if world == 1 and ob.available() and not args.no_cpu_baseline:
+            arena = rt.load_ray_file(*scene_files(wl))
+            orc = ob.Oracle(None, arena=arena)
+            r, s, desc = reference_sample(orc, params, w, h, args.cpu_seconds)
+            out["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": ob.ref().ref_get_threads(), "kind": "reference",
+                                   "sample": desc}
+        else:
+            out["cpu_baseline"] = None
+        print(json.dumps(out))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="host-core time spent on the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl, rank)
+    else:
+        run_b200(args, args.workload, wl, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -547,3 +547,169 @@ int ref_render_window(int w, int h, int i0, int i1, int j0, int j1, uint8_t* rgb
 }
 
 } // extern "C"
+
+// ---- a reference Scene built from an arena -------------------------------------------------------
+// RayTracer::loadScene on the 869,556-face dragon stand-in takes about 32 minutes in the reference
+// (KdTree's sort comparator copies the whole index vector each time it is passed by value,
+// kdTree.h:58-65).  The trace loop itself is what is being checked and timed, so for big scenes the
+// harness can instead populate the reference's OWN classes (Scene, Trimesh, TrimeshFace, KdTree,
+// Material, lights, camera) from an arena: same objects, same trees (tests prove the arena equals
+// what the reference builds), and every traversal / intersection / shading instruction that then
+// runs is the unmodified reference's.
+namespace {
+
+glm::dvec3 g3(const double* p) { return glm::dvec3(p[0], p[1], p[2]); }
+
+template <typename T>
+KdTree<T>* tree_from_arena(const std::vector<T>* items, const rt_node* nodes, const int32_t* its, int node)
+{
+	KdTree<T>* t = new KdTree<T>(items, std::vector<int>()); // the empty-index ctor path: no build
+	const rt_node& n = nodes[node];
+	t->bound = BoundingBox(g3(n.bmin), g3(n.bmax));
+	if (n.right < 0) {
+		for (int i = 0; i < n.count; i++) t->it_idxs.push_back(its[n.first + i]);
+	} else {
+		t->child[0] = tree_from_arena(items, nodes, its, node + 1);
+		t->child[1] = tree_from_arena(items, nodes, its, n.right);
+	}
+	return t;
+}
+
+TextureMap* texture_from_arena(const rt_texture& T, const uint8_t* texdata)
+{
+	TextureMap* t = (TextureMap*)::operator new(sizeof(TextureMap));
+	new (&t->data) std::vector<uint8_t>(texdata + T.offset, texdata + T.offset + (size_t)T.width * T.height * 3);
+	t->width = T.width;
+	t->height = T.height;
+	return t;
+}
+
+Material* material_from_arena(const rt_material& m, const std::vector<TextureMap*>& tex)
+{
+	Material* M = new Material();
+	MaterialParameter* ps[RT_NPARAM] = {&M->_ke, &M->_ka, &M->_ks, &M->_kd, &M->_kr, &M->_kt, &M->_bump};
+	for (int k = 0; k < RT_NPARAM; k++) {
+		ps[k]->_value = g3(m.k[k]);
+		ps[k]->_textureMap = m.tex[k] >= 0 ? tex[m.tex[k]] : nullptr;
+	}
+	M->_shininess._value = glm::dvec3(m.shininess_raw);
+	M->_shininess._textureMap = m.shininess_tex >= 0 ? tex[m.shininess_tex] : nullptr;
+	M->_index._value = glm::dvec3(m.index_raw);
+	M->_index._textureMap = m.index_tex >= 0 ? tex[m.index_tex] : nullptr;
+	M->_refl = m.refl != 0;
+	M->_trans = m.trans != 0;
+	M->_recur = m.recur != 0;
+	M->_spec = false;
+	M->_both = M->_refl && M->_trans;
+	return M;
+}
+
+} // namespace
+
+extern "C" int ref_load_arena(const void* arena, size_t bytes)
+{
+	ensure_globals();
+	(void)bytes;
+	rt::ArenaView A(arena);
+	const uint8_t* texdata = A.ptr<uint8_t>(RT_SEC_TEXDATA);
+	std::vector<TextureMap*> tex;
+	for (uint64_t k = 0; k < A.count(RT_SEC_TEXTURES); k++) tex.push_back(texture_from_arena(A.ptr<rt_texture>(RT_SEC_TEXTURES)[k], texdata));
+	const rt_material* mats = A.ptr<rt_material>(RT_SEC_MATERIALS);
+	const rt_globals& G = *A.ptr<rt_globals>(RT_SEC_GLOBALS);
+
+	g_ui->cubemap.reset();
+	g_ui->m_usingCubeMap = false;
+	if (G.has_cubemap) {
+		g_ui->setCubeMap(new CubeMap());
+		for (int k = 0; k < 6; k++) {
+			// each face gets its own copy: CubeMap owns its TextureMaps
+			const rt_texture& T = A.ptr<rt_texture>(RT_SEC_TEXTURES)[G.cubemap[k]];
+			g_ui->cubemap->setNthMap(k, texture_from_arena(T, texdata));
+		}
+		g_ui->useCubeMap(true);
+	}
+
+	Scene* sc = new Scene();
+	const rt_camera& C = *A.ptr<rt_camera>(RT_SEC_CAMERA);
+	sc->camera.eye = g3(C.eye);
+	sc->camera.look = g3(C.look);
+	sc->camera.u = g3(C.u);
+	sc->camera.v = g3(C.v);
+	sc->camera.aspectRatio = C.aspect;
+	sc->ambientIntensity = g3(G.ambient);
+
+	const rt_light* L = A.ptr<rt_light>(RT_SEC_LIGHTS);
+	for (uint64_t k = 0; k < A.count(RT_SEC_LIGHTS); k++) {
+		if (L[k].type == RT_LIGHT_POINT) {
+			sc->add(new PointLight(sc, g3(L[k].position), g3(L[k].color), (float)L[k].atten[0], (float)L[k].atten[1], (float)L[k].atten[2]));
+		} else if (L[k].type == RT_LIGHT_DIRECTIONAL) {
+			DirectionalLight* d = new DirectionalLight(sc, g3(L[k].orientation), g3(L[k].color));
+			d->orientation = g3(L[k].orientation); // the ctor would normalise a second time
+			sc->add(d);
+		} else {
+			return 2; // area / spot lights: load those scenes from their .ray text
+		}
+	}
+
+	const rt_object* O = A.ptr<rt_object>(RT_SEC_OBJECTS);
+	const rt_mesh* Ms = A.ptr<rt_mesh>(RT_SEC_MESHES);
+	const rt_face* F = A.ptr<rt_face>(RT_SEC_FACES);
+	const double* V = A.ptr<double>(RT_SEC_VERTS);
+	const double* VN = A.ptr<double>(RT_SEC_VNORMALS);
+	const int32_t* VM = A.ptr<int32_t>(RT_SEC_VMATS);
+	for (uint64_t k = 0; k < A.count(RT_SEC_OBJECTS); k++) {
+		const rt_object& o = O[k];
+		TransformNode* tn = sc->transformRoot.createChild(glm::dmat4x4(1.0));
+		for (int c = 0; c < 4; c++)
+			for (int r = 0; r < 4; r++) tn->inverse[c][r] = o.inv[c * 4 + r];
+		for (int c = 0; c < 3; c++)
+			for (int r = 0; r < 3; r++) tn->normi[c][r] = o.normi[c * 3 + r];
+		Material* mat = material_from_arena(mats[o.material], tex);
+		Geometry* g = nullptr;
+		switch (o.type) {
+		case RT_OBJ_SPHERE: g = new Sphere(sc, mat); break;
+		case RT_OBJ_BOX: g = new Box(sc, mat); break;
+		case RT_OBJ_SQUARE: g = new Square(sc, mat); break;
+		case RT_OBJ_CYLINDER: g = new Cylinder(sc, mat); break;
+		case RT_OBJ_CONE: {
+			Cone* cn = new Cone(sc, mat, o.cone[0], o.cone[1], o.cone[2], o.capped != 0);
+			cn->beta_squared = o.cone[3];
+			cn->gamma = o.cone[4];
+			g = cn;
+			break;
+		}
+		case RT_OBJ_TRIMESH: {
+			const rt_mesh& M = Ms[o.mesh];
+			Trimesh* tm = new Trimesh(sc, mat, tn);
+			tm->vertices.reserve(M.vert_cnt);
+			for (uint64_t v = 0; v < M.vert_cnt; v++) tm->vertices.push_back(g3(V + 3 * (M.vert_off + v)));
+			if (M.vnorm_off >= 0)
+				for (uint64_t v = 0; v < M.vert_cnt; v++) tm->normals.push_back(g3(VN + 3 * (M.vnorm_off + v)));
+			if (M.vmat_off >= 0)
+				for (uint64_t v = 0; v < M.vert_cnt; v++) tm->materials.push_back(material_from_arena(mats[VM[M.vmat_off + v]], tex));
+			tm->faces.reserve(M.face_cnt);
+			for (uint64_t f = 0; f < M.face_cnt; f++) {
+				const rt_face& fr = F[M.face_off + f];
+				TrimeshFace* face = new TrimeshFace(sc, new Material(*mat), tm, fr.ids[0], fr.ids[1], fr.ids[2]);
+				face->setTransform(tn);
+				tm->faces.push_back(face);
+			}
+			tm->kdtree = tree_from_arena(&tm->faces, A.ptr<rt_node>(RT_SEC_MESH_NODES) + M.node_off, A.ptr<int32_t>(RT_SEC_MESH_ITEMS) + M.item_off, 0);
+			g = tm;
+			break;
+		}
+		default: return 3;
+		}
+		g->setTransform(tn);
+		g->bounds = BoundingBox(g3(o.bbox), g3(o.bbox + 3));
+		sc->objects.emplace_back(g);
+	}
+	sc->kdtree = tree_from_arena(&sc->objects, A.ptr<rt_node>(RT_SEC_SCENE_NODES), A.ptr<int32_t>(RT_SEC_SCENE_ITEMS), 0);
+
+	delete theRayTracer;
+	theRayTracer = new RayTracer();
+	g_ui->setRayTracer(theRayTracer);
+	theRayTracer->scene.reset(sc);
+	g_ids.clear();
+	return 0;
+}

@@ -6,7 +6,8 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librt_b200.so")
+# RT_B200_LIB: alternative build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("RT_B200_LIB", os.path.join(HERE, "librt_b200.so"))
 
 RT_AA_NONE, RT_AA_SUPERSAMPLE, RT_AA_ADAPTIVE, RT_AA_JITTERED = 0, 1, 2, 3
 _STATUS = {1: "RT_ERR_ARG", 2: "RT_ERR_CUDA", 3: "RT_ERR_NO_DEVICE", 4: "RT_ERR_NO_SCENE", 5: "RT_ERR_IO",
@@ -88,6 +89,8 @@ def lib():
                                    ctypes.POINTER(vp), ctypes.POINTER(Stats)]
     L.rt_trace_pixels.argtypes = [vp, ctypes.POINTER(Params), ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, vp]
     L.rt_trace_rays.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, ctypes.c_int, vp, vp]
+    L.rt_selftest_division.argtypes = [vp, ctypes.c_longlong, ctypes.c_ulonglong, ctypes.c_int, ctypes.POINTER(ctypes.c_ulonglong)]
+    L.rt_selftest_division.restype = i32
     L.rt_load_ray_file.argtypes = [cp, vp, ctypes.POINTER(vp), ctypes.POINTER(sz)]
     L.rt_arena_free.argtypes = [vp]
     L.rt_arena_free.restype = None
@@ -197,6 +200,11 @@ class Context:
         dev = ctypes.c_void_p()
         self._check(lib().rt_render_device(self._h, ctypes.byref(params), w, h, part, n_parts, ctypes.byref(dev), ctypes.byref(st)))
         return dev.value, st
+
+    def selftest_division(self, n, seed=1, exp_range=40):
+        bad = ctypes.c_ulonglong()
+        self._check(lib().rt_selftest_division(self._h, n, seed, exp_range, ctypes.byref(bad)))
+        return bad.value
 
     def trace_pixels(self, params, w, h, ij):
         ij = np.ascontiguousarray(ij, dtype=np.int32).reshape(-1, 2)

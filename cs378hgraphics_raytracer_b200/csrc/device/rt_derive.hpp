@@ -10,6 +10,9 @@
 namespace rtd {
 
 struct Derived {
+	std::vector<DNode2> snodes2, mnodes2;
+	DTree stree;
+	std::vector<DTree> mtrees;
 	std::vector<DTri> tris;
 	std::vector<double> mesh_slack;
 	double scene_slack = 1e-9;
@@ -32,6 +35,31 @@ inline int tree_depth(const rt_node* n, uint64_t cnt)
 	return best;
 }
 
+// pre-order rt_node array (internal: child0 = k+1, child1 = right) -> DNode2 array of the internal
+// nodes only, same pre-order; leaves become references
+inline void build_nodes2(const rt_node* n, uint64_t cnt, std::vector<DNode2>& out, DTree& tree)
+{
+	tree.node_off = (int64_t)out.size();
+	for (int a = 0; a < 3; a++) { tree.lo[a] = cnt ? n[0].bmin[a] : 0.0; tree.hi[a] = cnt ? n[0].bmax[a] : 0.0; }
+	tree.pad = 0;
+	std::vector<int32_t> ref(cnt);
+	int32_t internal = 0;
+	for (uint64_t k = 0; k < cnt; k++) ref[k] = n[k].right >= 0 ? internal++ : leaf_ref(n[k].first, n[k].count);
+	tree.root = cnt ? ref[0] : leaf_ref(0, 0);
+	out.resize(out.size() + internal);
+	DNode2* dst = out.data() + tree.node_off;
+	for (uint64_t k = 0; k < cnt; k++) {
+		if (n[k].right < 0) continue;
+		DNode2& d = dst[ref[k]];
+		const rt_node& a = n[k + 1];
+		const rt_node& b = n[n[k].right];
+		for (int c = 0; c < 3; c++) { d.lo0[c] = a.bmin[c]; d.hi0[c] = a.bmax[c]; d.lo1[c] = b.bmin[c]; d.hi1[c] = b.bmax[c]; }
+		d.c0 = ref[k + 1];
+		d.c1 = ref[n[k].right];
+		for (int c = 0; c < 6; c++) d.pad[c] = 0;
+	}
+}
+
 inline double box_extent(const rt_node& n)
 {
 	double m = 1.0;
@@ -51,6 +79,7 @@ inline void derive(const rt::ArenaView& A, Derived& D)
 	const rt_node* mnodes = A.ptr<rt_node>(RT_SEC_MESH_NODES);
 	D.tris.resize(A.count(RT_SEC_MESH_ITEMS));
 	D.mesh_slack.resize(A.count(RT_SEC_MESHES));
+	D.mtrees.resize(A.count(RT_SEC_MESHES));
 	for (uint64_t m = 0; m < A.count(RT_SEC_MESHES); m++) {
 		const rt_mesh& M = meshes[m];
 		for (uint64_t k = 0; k < M.item_cnt; k++) {
@@ -66,11 +95,13 @@ inline void derive(const rt::ArenaView& A, Derived& D)
 		// slack: far above the rounding of a computed hit point (ulp(extent) ~ 2e-16*extent),
 		// far below any geometric feature
 		D.mesh_slack[m] = 1e-9 * box_extent(mnodes[M.node_off]);
+		build_nodes2(mnodes + M.node_off, M.node_cnt, D.mnodes2, D.mtrees[m]);
 		int d = tree_depth(mnodes + M.node_off, M.node_cnt);
 		if (d > D.max_mesh_depth) D.max_mesh_depth = d;
 	}
 	const rt_node* snodes = A.ptr<rt_node>(RT_SEC_SCENE_NODES);
 	D.scene_slack = 1e-9 * box_extent(snodes[0]);
+	build_nodes2(snodes, A.count(RT_SEC_SCENE_NODES), D.snodes2, D.stree);
 	D.max_scene_depth = tree_depth(snodes, A.count(RT_SEC_SCENE_NODES));
 }
 

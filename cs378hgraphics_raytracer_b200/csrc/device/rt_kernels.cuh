@@ -71,165 +71,9 @@ __device__ __forceinline__ bool grid_sample(const PoolArgs& A, long long sample,
 	return true;
 }
 
-__device__ __forceinline__ void pool_store(const PoolArgs& A, double* pd, int* pi, int slot, const RayTask& t, int sample)
-{
-	const int cap = A.cap;
-	pd[0 * cap + slot] = t.o.x; pd[1 * cap + slot] = t.o.y; pd[2 * cap + slot] = t.o.z;
-	pd[3 * cap + slot] = t.d.x; pd[4 * cap + slot] = t.d.y; pd[5 * cap + slot] = t.d.z;
-	pd[6 * cap + slot] = t.weight.x; pd[7 * cap + slot] = t.weight.y; pd[8 * cap + slot] = t.weight.z;
-	pd[9 * cap + slot] = t.att_kt.x; pd[10 * cap + slot] = t.att_kt.y; pd[11 * cap + slot] = t.att_kt.z;
-	pi[0 * cap + slot] = sample;
-	pi[1 * cap + slot] = t.depth | (t.att_mode << 8) | (t.kind << 12);
-}
-__device__ __forceinline__ void pool_load(const PoolArgs& A, const double* pd, const int* pi, int slot, RayTask& t, int& sample)
-{
-	const int cap = A.cap;
-	t.o = mk3(pd[0 * cap + slot], pd[1 * cap + slot], pd[2 * cap + slot]);
-	t.d = mk3(pd[3 * cap + slot], pd[4 * cap + slot], pd[5 * cap + slot]);
-	t.weight = mk3(pd[6 * cap + slot], pd[7 * cap + slot], pd[8 * cap + slot]);
-	t.att_kt = mk3(pd[9 * cap + slot], pd[10 * cap + slot], pd[11 * cap + slot]);
-	sample = pi[0 * cap + slot];
-	const int m = pi[1 * cap + slot];
-	t.depth = m & 255;
-	t.att_mode = (m >> 8) & 15;
-	t.kind = (m >> 12) & 15;
-}
-
-#ifndef RT_POOL_THREADS
-#define RT_POOL_THREADS 128
-#endif
-
-__global__ void __launch_bounds__(RT_POOL_THREADS) k_trace_pool(const DScene S, const PoolArgs A)
-{
-	const unsigned lane = threadIdx.x & 31;
-	const unsigned lt_mask = (1u << lane) - 1u;
-	const long long warp_global = (long long)blockIdx.x * (RT_POOL_THREADS / 32) + (threadIdx.x >> 5);
-	double* pd = A.pool_d + warp_global * (long long)A.cap * RT_POOL_DOUBLES;
-	int* pi = A.pool_i + warp_global * (long long)A.cap * 2;
-
-	int count = 0;                  // entries in this warp's pool (warp-uniform)
-	long long cam_next = 0, cam_end = 0; // reserved slice of the global cursor (warp-uniform)
-	bool exhausted = false;
-	bool has_task = false;
-	RayTask task;
-	int sample = 0;
-	unsigned n_cam = 0, n_refl = 0, n_refr = 0, n_shadow = 0, overflow = 0;
-
-	for (;;) {
-		// ---- refill idle lanes: pool first, then fresh primaries --------------------------------
-		const unsigned idle_mask = __ballot_sync(0xffffffffu, !has_task);
-		int n_idle = __popc(idle_mask);
-		if (n_idle) {
-			const int rank = __popc(idle_mask & lt_mask);
-			const int take = n_idle < count ? n_idle : count;
-			if (!has_task && rank < take) {
-				pool_load(A, pd, pi, count - 1 - rank, task, sample);
-				has_task = true;
-			}
-			count -= take;
-			int need = n_idle - take;
-			int served = take;
-			while (need > 0 && !exhausted) {
-				if (cam_next >= cam_end) {
-					unsigned long long base = 0;
-					if (lane == 0) base = atomicAdd(A.cursor, (unsigned long long)RT_CHUNK);
-					base = __shfl_sync(0xffffffffu, base, 0);
-					if ((long long)base >= A.n_slots) { exhausted = true; break; }
-					cam_next = (long long)base;
-					cam_end = cam_next + RT_CHUNK < A.n_slots ? cam_next + RT_CHUNK : A.n_slots;
-				}
-				const int avail = (int)(cam_end - cam_next);
-				const int give = need < avail ? need : avail;
-				if (!has_task && rank >= served && rank < served + give) {
-					const long long slot = cam_next + (rank - served);
-					const long long smp = slot / A.lenses;
-					const int lens = (int)(slot % A.lenses);
-					bool ok = true;
-					if (A.src == SRC_RAYS) {
-						task.o = ld3(A.rays[slot].p);
-						task.d = ld3(A.rays[slot].d);
-					} else {
-						double x, y;
-						if (A.src == SRC_GRID) {
-							int pi_, pj_;
-							ok = grid_sample(A, smp, pi_, pj_, x, y);
-						} else {
-							x = A.xs[smp];
-							y = A.ys[smp];
-						}
-						if (ok) primary_ray(S.cam, A.prm, x, y, lens, A.eye_shift, task.o, task.d);
-					}
-					if (ok) {
-						task.weight = mk3(1.0, 1.0, 1.0);
-						task.att_kt = mk3(1.0, 1.0, 1.0);
-						task.att_mode = 0;
-						task.depth = A.depth;
-						task.kind = 0;
-						sample = (int)smp;
-						has_task = true;
-					}
-				}
-				cam_next += give;
-				served += give;
-				need -= give;
-			}
-		}
-		if (!__any_sync(0xffffffffu, has_task)) {
-			if (exhausted && count == 0) break;
-			continue;
-		}
-		// ---- trace + shade one ray per lane -----------------------------------------------------
-		RayTask kids[2];
-		int n_kids = 0;
-		if (has_task) {
-			Hit h;
-			unsigned sh = 0;
-			const d3 c = trace_step<true>(S, A.prm, task, h, kids, n_kids, sh);
-			n_shadow += sh;
-			if (task.kind == 0) n_cam++;
-			else if (task.kind == 1) n_refl++;
-			else n_refr++;
-			double* acc = A.accum + 3ll * sample;
-			if (c.x != 0.0) atomicAdd(acc + 0, c.x);
-			if (c.y != 0.0) atomicAdd(acc + 1, c.y);
-			if (c.z != 0.0) atomicAdd(acc + 2, c.z);
-		}
-		// ---- push children: warp-scan compaction into the pool ----------------------------------
-		int incl = n_kids;
-#pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			const int v = __shfl_up_sync(0xffffffffu, incl, o);
-			if ((int)lane >= o) incl += v;
-		}
-		const int total = __shfl_sync(0xffffffffu, incl, 31);
-		if (total) {
-			if (count + total > A.cap) {
-				overflow = 1; // never expected (cap = 32*(depth+3)); reported through stats[4]
-			} else {
-				const int base = count + incl - n_kids;
-				for (int k = 0; k < n_kids; k++) pool_store(A, pd, pi, base + k, kids[k], sample);
-				count += total;
-			}
-		}
-		has_task = false;
-	}
-	// ---- ray counters ------------------------------------------------------------------------------
-#pragma unroll
-	for (int o = 16; o > 0; o >>= 1) {
-		n_cam += __shfl_down_sync(0xffffffffu, n_cam, o);
-		n_refl += __shfl_down_sync(0xffffffffu, n_refl, o);
-		n_refr += __shfl_down_sync(0xffffffffu, n_refr, o);
-		n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
-		overflow |= __shfl_down_sync(0xffffffffu, overflow, o);
-	}
-	if (lane == 0) {
-		if (n_cam) atomicAdd(A.stats + 0, (unsigned long long)n_cam);
-		if (n_refl) atomicAdd(A.stats + 1, (unsigned long long)n_refl);
-		if (n_refr) atomicAdd(A.stats + 2, (unsigned long long)n_refr);
-		if (n_shadow) atomicAdd(A.stats + 3, (unsigned long long)n_shadow);
-		if (overflow) atomicAdd(A.stats + 4, 1ull);
-	}
-}
+} // namespace rtd
+#include "rt_pool.cuh"
+namespace rtd {
 
 // ---- Scene::intersect for caller-supplied rays (rt_trace_rays hits) ---------------------------
 __global__ void __launch_bounds__(128) k_hits(const DScene S, const rt_ray* rays, int n, rt_hit* out)
@@ -412,5 +256,35 @@ __global__ void __launch_bounds__(256) k_sample_values(const double* accum, cons
 	out[3 * k] = c.x;
 	out[3 * k + 1] = c.y;
 	out[3 * k + 2] = c.z;
+}
+} // namespace rtd
+
+namespace rtd {
+// Self-test of div_by (rt_math.cuh) against the hardware IEEE division sequence: pseudo-random
+// operands (full random mantissas; every 4th divisor gets a mantissa of all ones or a single bit,
+// the hard cases of reciprocal-based division).  Counts quotients that differ in any bit.
+__device__ __forceinline__ unsigned long long splitmix(unsigned long long& s)
+{
+	unsigned long long z = (s += 0x9e3779b97f4a7c15ull);
+	z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+	z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+	return z ^ (z >> 31);
+}
+__global__ void __launch_bounds__(256) k_div_selftest(unsigned long long seed, long long n, int exp_range, unsigned long long* mismatches)
+{
+	const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	unsigned long long s = seed + 0x632be59bd9b4e019ull * (unsigned long long)k;
+	unsigned long long ma = splitmix(s), md = splitmix(s), e = splitmix(s);
+	const int ea = (int)(e % (2 * exp_range + 1)) - exp_range, ed = (int)((e >> 20) % (2 * exp_range + 1)) - exp_range;
+	if ((k & 3) == 1) md = ~0ull;
+	if ((k & 3) == 2) md = 1ull << (e >> 58);
+	if ((k & 15) == 7) ma = 0;
+	const unsigned long long sa = (ma >> 63) << 63, sd = (md >> 62) << 63;
+	const double a = __longlong_as_double(sa | ((unsigned long long)(1023 + ea) << 52) | (ma & 0xfffffffffffffull));
+	const double d = __longlong_as_double(sd | ((unsigned long long)(1023 + ed) << 52) | (md & 0xfffffffffffffull));
+	const double y = 1.0 / d;
+	const double q1 = div_by(a, d, y), q2 = a / d;
+	if (__double_as_longlong(q1) != __double_as_longlong(q2)) atomicAdd(mismatches, 1ull);
 }
 } // namespace rtd

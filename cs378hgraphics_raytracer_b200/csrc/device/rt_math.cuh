@@ -66,6 +66,40 @@ RT_HD d3 mul33(const double* m, d3 v)
 	           m[2] * v.x + m[5] * v.y + m[8] * v.z);
 }
 
+// ---- IEEE division by a per-ray constant, without the ~25-instruction DDIV sequence --------------
+// The slab test divides six numbers per box by the three direction components.  With y = 1.0/d
+// (one real division per axis per ray) Markstein's correction recovers the CORRECTLY ROUNDED
+// quotient a/d from FMAs: q0 = a*y is within 2 ulp; r0 = a - q0*d is exact in an FMA; q1 = q0 + r0*y
+// is faithful; one more step (r1, q2) is the correctly rounded a/d (Markstein 1990; Muller et al.,
+// Handbook of Floating-Point Arithmetic, "division with an FMA").  The proof needs no overflow or
+// underflow in the intermediates, hence the range guards; outside them (never seen in practice) the
+// real division runs.  tests/test_gpu_parity.py::test_division_selftest compares 2^28 quotients
+// against the hardware sequence bit for bit.
+struct RayInv {
+	d3 y;    // 1/d per axis (IEEE)
+	d3 sl;   // pruning slack per axis = slack/|d|
+	bool slow; // some |d| outside [2^-300, 2^300]: use real divisions
+};
+RT_HD bool div_range_ok(double d) { const double a = fabs(d); return d == 0.0 || (a >= 0x1p-300 && a <= 0x1p300); }
+RT_HD RayInv make_inv(const d3& d, double slack)
+{
+	RayInv I;
+	I.y = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
+	I.sl = mk3(slack * fabs(I.y.x), slack * fabs(I.y.y), slack * fabs(I.y.z));
+	I.slow = !(div_range_ok(d.x) && div_range_ok(d.y) && div_range_ok(d.z));
+	return I;
+}
+RT_HD double div_by(double a, double d, double y)
+{
+	const double m = fabs(a);
+	if (!(m <= 0x1p600) || (m < 0x1p-600 && a != 0.0)) return a / d;
+	double q = a * y;
+	double r = fma(-q, d, a);
+	q = fma(r, y, q);
+	r = fma(-q, d, a);
+	return fma(r, y, q);
+}
+
 #define RT_RAY_EPSILON 0.00000001
 #define RT_EPS32 (RT_RAY_EPSILON / 32)
 

@@ -7,24 +7,27 @@ namespace rtd {
 
 // BoundingBox::intersect (reference ray/src/scene/bbox.cc:33-70).  The per-axis early returns
 // are monotone (tMin only grows, tMax only shrinks) so testing once after the loop is identical.
+// The six quotients come from div_by (rt_math.cuh): bit-identical to IEEE division.
 // `entry` receives tMin lowered by sl = slack/|d| per axis (precomputed per ray): a conservative entry distance used ONLY to
 // cull subtrees that cannot beat the current closest hit; box membership itself is decided by the
 // reference's exact arithmetic (see DESIGN.md "pruning without changing the winner").
-RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3& d, const d3& sl, double& entry)
+RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
 {
 	double tMin = -1.0e308, tMax = 1.0e308, en = -1.0e308;
-#define RT_SLAB(O, D, LO, HI, SL)                      \
-	if (D != 0.0) {                                    \
-		double t1 = (LO - O) / D, t2 = (HI - O) / D;   \
-		if (t1 > t2) { double tt = t1; t1 = t2; t2 = tt; } \
-		if (t1 > tMin) tMin = t1;                      \
-		if (t2 < tMax) tMax = t2;                      \
-		double e = t1 - SL;                            \
-		if (e > en) en = e;                            \
+#define RT_SLAB(O, D, Y, LO, HI, SL)                                        \
+	if (D != 0.0) {                                                         \
+		double t1, t2;                                                      \
+		if (I.slow) { t1 = (LO - O) / D; t2 = (HI - O) / D; }               \
+		else { t1 = div_by(LO - O, D, Y); t2 = div_by(HI - O, D, Y); }      \
+		if (t1 > t2) { double tt = t1; t1 = t2; t2 = tt; }                  \
+		if (t1 > tMin) tMin = t1;                                           \
+		if (t2 < tMax) tMax = t2;                                           \
+		double e = t1 - SL;                                                 \
+		if (e > en) en = e;                                                 \
 	}
-	RT_SLAB(o.x, d.x, bmin[0], bmax[0], sl.x)
-	RT_SLAB(o.y, d.y, bmin[1], bmax[1], sl.y)
-	RT_SLAB(o.z, d.z, bmin[2], bmax[2], sl.z)
+	RT_SLAB(o.x, d.x, I.y.x, bmin[0], bmax[0], I.sl.x)
+	RT_SLAB(o.y, d.y, I.y.y, bmin[1], bmax[1], I.sl.y)
+	RT_SLAB(o.z, d.z, I.y.z, bmin[2], bmax[2], I.sl.z)
 #undef RT_SLAB
 	entry = en;
 	if (tMin > tMax) return false;

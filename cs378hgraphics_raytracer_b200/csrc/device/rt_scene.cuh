@@ -16,7 +16,35 @@ struct DTri {
 	double v0[3], v1[3], v2[3], n[3];
 };
 
+// Traversal node: one 128-byte record per INTERNAL node of a reference tree holding BOTH children's
+// boxes, so one step of the walk is one aligned 128-byte read (eight 128-bit loads) instead of three
+// scattered node reads.  A child reference is >= 0 for an internal node (index into the same
+// array, relative to the tree) or a leaf reference < 0 that encodes the leaf's item range.
+// Child 0 / child 1 keep the reference's order (kdTree.h:111-112).
+struct alignas(128) DNode2 {
+	double lo0[3], hi0[3]; // child[0] bounds
+	double lo1[3], hi1[3]; // child[1] bounds
+	int32_t c0, c1;
+	int32_t pad[6];
+};
+#define RT_REF_MESH_EXIT ((int32_t)0x80000000)
+#define RT_REF_NONE ((int32_t)0x80000001)
+RT_HD int32_t leaf_ref(int32_t first, int32_t count) { return -(1 + ((first << 2) | count)); }
+RT_HD int32_t leaf_first(int32_t ref) { return (-(ref + 1)) >> 2; }
+RT_HD int32_t leaf_count(int32_t ref) { return (-(ref + 1)) & 3; }
+
+struct DTree {
+	double lo[3], hi[3]; // root bounds
+	int32_t root;        // root reference (a leaf reference for trees of <= 3 items)
+	int32_t pad;
+	int64_t node_off;    // first DNode2 of this tree
+};
+
 struct DScene {
+	const DNode2* snodes2;
+	DTree stree;
+	const DNode2* mnodes2;
+	const DTree* mtrees; // per mesh
 	const rt_node* snodes;
 	const int32_t* sitems;
 	const rt_object* objs;

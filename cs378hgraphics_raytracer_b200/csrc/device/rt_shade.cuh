@@ -1,6 +1,6 @@
 // rt_shade.cuh - camera rays, Phong shading and the one-bounce step of RayTracer::traceRay.
 #pragma once
-#include "rt_shadow.cuh"
+#include "rt_traverse.cuh"
 
 namespace rtd {
 
@@ -40,35 +40,43 @@ RT_HD void primary_ray(const rt_camera& C, const rt_params& prm, double x, doubl
 	d = normalize(dest - o);
 }
 
-// Material::shade (reference scene/material.cpp:34-69) with PointLight/DirectionalLight
-// (scene/light.cpp:56-73).  shadow_rays counts Scene::intersectList calls.
+// One light's term of Material::shade (reference scene/material.cpp:50-66) with PointLight /
+// DirectionalLight (scene/light.cpp:56-73): everything except the shadow attenuation, plus the
+// shadow ray Light::shadowAttenuation would trace (light.cpp:16-20: origin backed up along the
+// view ray by 1e-10, aimed at the light).  term = (dattn * Lc) * (d_comp + s_comp).
+RT_HD void light_term(const rt_light& L, const MatEval& m, const d3& P, const d3& N, const d3& view, d3& term, d3& pb, d3& sdir)
+{
+	const bool point = L.type != RT_LIGHT_DIRECTIONAL;
+	const d3 lpos = ld3(L.position);
+	const d3 l_i = point ? normalize(lpos - P) : -ld3(L.orientation);
+	const d3 l_r = l_i - (2 * dot(l_i, N)) * N;
+	double dt = dot(l_i, N);
+	if (m.trans) dt = fabs(dt);
+	const d3 d_comp = m.kd * gmax(0.0, dt);
+	const double sp = pow(gmax(0.0, dot(l_r, view)), m.shininess);
+	const d3 s_comp = m.ks * sp;
+	double dattn = 1.0;
+	if (point) {
+		const double dist = length(P - lpos);
+		dattn = gclamp(1.0 / (L.atten[0] + L.atten[1] * dist + L.atten[2] * dist * dist), 0.0, 1.0);
+	}
+	pb = P - view * 0.0000000001;
+	sdir = point ? normalize(lpos - pb) : -ld3(L.orientation);
+	term = (dattn * ld3(L.color)) * (d_comp + s_comp);
+}
+
+// Material::shade with the shadow rays traced inline.  shadow_rays counts Scene::intersectList calls.
 RT_HD d3 shade(const DScene& S, const rt_params& prm, const MatEval& m, const d3& o, const d3& d, const Hit& h, unsigned& shadow_rays)
 {
 	const d3 P = o + h.t * d;
-	const d3 N = h.N;
 	d3 out = m.ke + m.ka * ld3(S.glob.ambient);
 	for (int li = 0; li < S.n_lights; li++) {
 		const rt_light& L = S.lights[li];
-		const bool point = L.type != RT_LIGHT_DIRECTIONAL;
-		const d3 lpos = ld3(L.position);
-		const d3 l_i = point ? normalize(lpos - P) : -ld3(L.orientation);
-		const d3 l_r = l_i - (2 * dot(l_i, N)) * N;
-		double dt = dot(l_i, N);
-		if (m.trans) dt = fabs(dt);
-		const d3 d_comp = m.kd * gmax(0.0, dt);
-		const double sp = pow(gmax(0.0, dot(l_r, d)), m.shininess);
-		const d3 s_comp = m.ks * sp;
-		double dattn = 1.0;
-		if (point) {
-			const double dist = length(P - lpos);
-			dattn = gclamp(1.0 / (L.atten[0] + L.atten[1] * dist + L.atten[2] * dist * dist), 0.0, 1.0);
-		}
-		// Light::shadowAttenuation (light.cpp:16-20): back up along the view ray, aim at the light
-		const d3 pb = P - d * 0.0000000001;
-		const d3 sdir = point ? normalize(lpos - pb) : -ld3(L.orientation);
+		d3 term, pb, sdir;
+		light_term(L, m, P, h.N, d, term, pb, sdir);
 		shadow_rays++;
 		const d3 sattn = shadow_attenuation(S, L, pb, sdir, prm);
-		out = out + ((dattn * sattn) * ld3(L.color)) * (d_comp + s_comp);
+		out = out + sattn * term;
 	}
 	return out;
 }
@@ -85,77 +93,99 @@ struct RayTask {
 	int kind;  // 0 camera, 1 reflection, 2 refraction
 };
 
-// One call of RayTracer::traceRay without its recursion (reference RayTracer.cpp:108-174):
-// returns the colour this ray adds to its camera sample and fills up to two children.
-// Overlapping-objects mode is off here: the medium outside a surface is air (index 1, kt 1).
+// CubeMap::getColor (reference scene/cubeMap.cpp:12-44) for a ray that hit nothing; ties leave
+// map/d unset in the reference (UB), pinned by the oracle build to map 0, d = 0.
+RT_HD d3 miss_colour(const DScene& S, const rt_params& prm, const d3& rd)
+{
+	if (!(prm.use_cubemap && S.glob.has_cubemap)) return mk3(0.0, 0.0, 0.0);
+	const double ax = fabs(rd.x), ay = fabs(rd.y), az = fabs(rd.z);
+	const bool xy = ax >= ay, yz = ay >= az, zx = az >= ax;
+	int map = 0;
+	double scale = 0.5;
+	d2 dd; dd.x = 0.0; dd.y = 0.0;
+	if (xy && !zx) { scale /= ax; dd.x = rd.x > 0 ? rd.z : -rd.z; dd.y = rd.y; map = rd.x > 0 ? 0 : 1; }
+	else if (yz && !xy) { scale /= ay; dd.x = rd.x; dd.y = rd.y > 0 ? rd.z : -rd.z; map = rd.y > 0 ? 2 : 3; }
+	else if (zx && !yz) { scale /= az; dd.x = rd.z > 0 ? rd.x : -rd.x; dd.y = rd.y; map = rd.z > 0 ? 4 : 5; }
+	dd.x = dd.x * scale + 0.5;
+	dd.y = dd.y * scale + 0.5;
+	return tex_sample(S, S.glob.cubemap[map], dd);
+}
+
+// weight of a ray once its own hit distance is known (RayTracer.cpp:149,162)
+RT_HD d3 apply_att(const d3& w, const d3& att_kt, int att_mode, double t)
+{
+	if (att_mode == 1) return w * gclamp(vpow(att_kt, t), 0.0, 1.0);
+	if (att_mode == 2) return w * vpow(att_kt, t);
+	return w;
+}
+
+// The reflection / refraction rays of RayTracer::traceRay (reference RayTracer.cpp:127-165) for a
+// hit of ray (ro, rd) with weight w; depth is the already decremented depth.  Overlapping-objects
+// mode is off: the medium on the far side of a surface is air (index 1, kt 1; material.cpp:17-21).
+// kid[0] = reflection (valid if has_refl), kid[1] = refraction (valid if has_refr).
+RT_HD void spawn_children(const MatEval& m, const Hit& h, const d3& ro, const d3& rd, const d3& w, int depth, RayTask* kid, bool& has_refl, bool& has_refr)
+{
+	has_refl = has_refr = false;
+	if (!(m.recur && depth > 0)) return;
+	const bool leaving = dot(h.N, rd) >= 0;
+	const double air_index = intensity(mk3(1.0, 1.0, 1.0)); // air.index(i) goes through intensityValue too
+	const double idx_curr = leaving ? m.index : air_index, idx_next = leaving ? air_index : m.index;
+	const d3 kt_curr = leaving ? m.kt : mk3(1.0, 1.0, 1.0), kt_next = leaving ? mk3(1.0, 1.0, 1.0) : m.kt;
+	const bool next_trans = leaving ? true : m.trans;
+	const d3 normal = (leaving ? -1.0 : 1.0) * h.N;
+	const double c = -1 * dot(normal, rd);
+	const double eta = next_trans ? idx_curr / idx_next : 0;
+	const double radicand = 1 - eta * eta * (1 - c * c);
+	const bool tir = next_trans && radicand < 0;
+	if (m.refl || tir) {
+		RayTask& k = kid[0];
+		k.d = rd + (2 * c) * normal;
+		k.o = ro + (h.t - RT_RAY_EPSILON) * rd;
+		k.weight = w * m.kr;
+		k.att_kt = kt_curr;
+		k.att_mode = (kt_curr.x == 1.0 && kt_curr.y == 1.0 && kt_curr.z == 1.0) ? 0 : 1;
+		k.depth = depth;
+		k.kind = 1;
+		has_refl = true;
+	}
+	if (next_trans && !tir) {
+		RayTask& k = kid[1];
+		k.o = ro + (h.t + RT_RAY_EPSILON) * rd;
+		k.d = eta * rd + (eta * c - sqrt(radicand)) * normal;
+		k.weight = w;
+		k.att_kt = kt_next;
+		k.att_mode = (kt_next.x == 1.0 && kt_next.y == 1.0 && kt_next.z == 1.0) ? 0 : 2;
+		k.depth = depth;
+		k.kind = 2;
+		has_refr = true;
+	}
+}
+
+// One call of RayTracer::traceRay without its recursion (reference RayTracer.cpp:108-174), shadow
+// rays traced inline: returns the colour this ray adds to its camera sample and fills up to two
+// children.  (The wavefront kernel uses the same pieces but defers the shadow rays to the pool.)
 template <bool PRUNE>
 RT_HD d3 trace_step(const DScene& S, const rt_params& prm, const RayTask& r, Hit& h, RayTask* child, int& n_child, unsigned& shadow_rays)
 {
 	n_child = 0;
-	d3 w = r.weight;
 	if (!(r.depth >= 0 && closest_hit<PRUNE>(S, r.o, r.d, h))) {
 		// miss: the parent's exponent is the (pinned-to-zero) uninitialised length -> factor 1
 		h.obj = -1;
-		if (prm.use_cubemap && S.glob.has_cubemap) {
-			// CubeMap::getColor (reference scene/cubeMap.cpp:12-44); ties leave map/d unset (UB),
-			// pinned by the oracle build to map 0, d = 0
-			const d3 rd = r.d;
-			const double ax = fabs(rd.x), ay = fabs(rd.y), az = fabs(rd.z);
-			const bool xy = ax >= ay, yz = ay >= az, zx = az >= ax;
-			int map = 0;
-			double scale = 0.5;
-			d2 dd; dd.x = 0.0; dd.y = 0.0;
-			if (xy && !zx) { scale /= ax; dd.x = rd.x > 0 ? rd.z : -rd.z; dd.y = rd.y; map = rd.x > 0 ? 0 : 1; }
-			else if (yz && !xy) { scale /= ay; dd.x = rd.x; dd.y = rd.y > 0 ? rd.z : -rd.z; map = rd.y > 0 ? 2 : 3; }
-			else if (zx && !yz) { scale /= az; dd.x = rd.z > 0 ? rd.x : -rd.x; dd.y = rd.y; map = rd.z > 0 ? 4 : 5; }
-			dd.x = dd.x * scale + 0.5;
-			dd.y = dd.y * scale + 0.5;
-			return w * tex_sample(S, S.glob.cubemap[map], dd);
-		}
-		return mk3(0.0, 0.0, 0.0);
+		return r.weight * miss_colour(S, prm, r.d);
 	}
 	finalize_hit(S, r.o, r.d, h);
-	if (r.att_mode == 1) w = w * gclamp(vpow(r.att_kt, h.t), 0.0, 1.0) ;
-	else if (r.att_mode == 2) w = w * vpow(r.att_kt, h.t);
+	const d3 w = apply_att(r.weight, r.att_kt, r.att_mode, h.t);
 	const int depth = r.depth - 1;
 	MatEval m;
 	eval_material(S, h, m);
 	const d3 col = shade(S, prm, m, r.o, r.d, h, shadow_rays);
 	const d3 ret = w * col;
 	if (prm.aterm_thresh > 0.0 && dot(col, col) < prm.aterm_thresh) return ret;
-	if (m.recur && depth > 0) {
-		const bool leaving = dot(h.N, r.d) >= 0;
-		// curr/next media; `air` on the far side (material.cpp:17-21)
-		const double air_index = intensity(mk3(1.0, 1.0, 1.0)); // air.index(i) goes through intensityValue too
-		const double idx_curr = leaving ? m.index : air_index, idx_next = leaving ? air_index : m.index;
-		const d3 kt_curr = leaving ? m.kt : mk3(1.0, 1.0, 1.0), kt_next = leaving ? mk3(1.0, 1.0, 1.0) : m.kt;
-		const bool next_trans = leaving ? true : m.trans;
-		const d3 normal = (leaving ? -1.0 : 1.0) * h.N;
-		const double c = -1 * dot(normal, r.d);
-		const double eta = next_trans ? idx_curr / idx_next : 0;
-		const double radicand = 1 - eta * eta * (1 - c * c);
-		const bool tir = next_trans && radicand < 0;
-		if (m.refl || tir) {
-			RayTask& k = child[n_child++];
-			k.d = r.d + (2 * c) * normal;
-			k.o = r.o + (h.t - RT_RAY_EPSILON) * r.d;
-			k.weight = w * m.kr;
-			k.att_kt = kt_curr;
-			k.att_mode = (kt_curr.x == 1.0 && kt_curr.y == 1.0 && kt_curr.z == 1.0) ? 0 : 1;
-			k.depth = depth;
-			k.kind = 1;
-		}
-		if (next_trans && !tir) {
-			RayTask& k = child[n_child++];
-			k.o = r.o + (h.t + RT_RAY_EPSILON) * r.d;
-			k.d = eta * r.d + (eta * c - sqrt(radicand)) * normal;
-			k.weight = w;
-			k.att_kt = kt_next;
-			k.att_mode = (kt_next.x == 1.0 && kt_next.y == 1.0 && kt_next.z == 1.0) ? 0 : 2;
-			k.depth = depth;
-			k.kind = 2;
-		}
-	}
+	RayTask kid[2];
+	bool a, b;
+	spawn_children(m, h, r.o, r.d, w, depth, kid, a, b);
+	if (a) child[n_child++] = kid[0];
+	if (b) child[n_child++] = kid[1];
 	return ret;
 }
 

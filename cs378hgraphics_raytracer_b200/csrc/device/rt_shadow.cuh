@@ -190,208 +190,4 @@ template <typename F> RT_HD void cone_list(d3 R0, d3 Rd, const double* prm, int 
 	}
 }
 
-// Geometry::intersectList for one scene-level candidate (reference scene/scene.cpp:40-64)
-RT_HD void object_list(const DScene& S, int obj, unsigned rank, const d3& o, const d3& d, const d3& sl, SBuf& B, int* stk, double* stke, int sp0)
-{
-	const rt_object& ob = S.objs[obj];
-	double e;
-	if (!box_hit(ob.bbox, ob.bbox + 3, o, d, sl, e)) return;
-	if (e > B.cut) return;
-	const LocalRay L = to_local(ob, o, d);
-	if (ob.type != RT_OBJ_TRIMESH) {
-		const rt_material& m = S.mats[ob.material];
-		auto emit = [&](double tl, d3 Nl, d2 uv, int sub) {
-			const double t = tl / L.len;
-			if (!(t <= B.cut)) return;
-			const d3 N = world_normal(S, ob, Nl, uv);
-			const bool inside = dot(N, d) > 0;
-			sbuf_add(B, t, ((unsigned long long)rank << 32) | (unsigned)sub, inside, m.trans != 0, mat_param(S, m, RT_KT, uv));
-		};
-		switch (ob.type) {
-		case RT_OBJ_SPHERE: sphere_list(L.o, L.d, emit); break;
-		case RT_OBJ_BOX: box_list(L.o, L.d, emit); break;
-		case RT_OBJ_SQUARE: {
-			LocalHit h;
-			h.uv.x = h.uv.y = 0.0;
-			if (square_hit<true>(L.o, L.d, h)) emit(h.t, h.N, h.uv, 0);
-			break;
-		}
-		case RT_OBJ_CYLINDER: cylinder_list(L.o, L.d, emit); break;
-		case RT_OBJ_CONE: cone_list(L.o, L.d, ob.cone, ob.capped, emit); break;
-		default: break;
-		}
-		return;
-	}
-	// Trimesh::intersectLocalList (reference SceneObjects/trimesh.cpp:97-105): every face the
-	// per-mesh tree offers that the ray hits
-	const rt_mesh& M = S.meshes[ob.mesh];
-	const rt_node* nodes = S.mnodes + M.node_off;
-	const DTri* tris = S.tris + M.item_off;
-	const d3 lsl = slack_vec(L.d, S.mesh_slack[ob.mesh]);
-	double le;
-	if (!box_hit(nodes[0].bmin, nodes[0].bmax, L.o, L.d, lsl, le)) return;
-	int sp = sp0, node = 0;
-	for (;;) {
-		const double lcut = B.cut < RT_T_INF ? (B.cut * L.len) * (1.0 + 1e-9) + 1e-300 : RT_T_INF;
-		const rt_node& n = nodes[node];
-		bool descend = false;
-		if (n.right < 0) {
-			for (int i = 0; i < n.count; i++) {
-				const int pos = n.first + i;
-				double tl;
-				d3 bary;
-				if (!tri_hit<true>(tris[pos], L.o, L.d, tl, bary)) continue;
-				const double t = tl / L.len;
-				if (!(t <= B.cut)) continue;
-				Hit h;
-				h.obj = obj;
-				h.fpos = (int)M.item_off + pos;
-				h.face = S.mitems[h.fpos];
-				h.bary = bary;
-				h.uv.x = h.uv.y = 0.0;
-				const rt_face& f = S.faces[M.face_off + h.face];
-				d3 Nl;
-				if (M.vnorm_off >= 0) {
-					const double* n0 = S.vnormals + 3 * (M.vnorm_off + f.ids[0]);
-					const double* n1 = S.vnormals + 3 * (M.vnorm_off + f.ids[1]);
-					const double* n2 = S.vnormals + 3 * (M.vnorm_off + f.ids[2]);
-					Nl = normalize(mk3(n0[0] * bary.x + n1[0] * bary.y + n2[0] * bary.z,
-					                   n0[1] * bary.x + n1[1] * bary.y + n2[1] * bary.z,
-					                   n0[2] * bary.x + n1[2] * bary.y + n2[2] * bary.z));
-				} else {
-					Nl = ld3(f.normal);
-				}
-				const d3 N = normalize(mul33(ob.normi, Nl));
-				d3 kt;
-				bool trans;
-				eval_kt(S, h, kt, trans);
-				sbuf_add(B, t, ((unsigned long long)rank << 32) | (unsigned)pos, dot(N, d) > 0, trans, kt);
-			}
-		} else {
-			const int c0 = node + 1, c1 = n.right;
-			double e0, e1;
-			bool h0 = box_hit(nodes[c0].bmin, nodes[c0].bmax, L.o, L.d, lsl, e0) && !(e0 > lcut);
-			bool h1 = box_hit(nodes[c1].bmin, nodes[c1].bmax, L.o, L.d, lsl, e1) && !(e1 > lcut);
-			if (h0 && h1) {
-				const bool swap = e1 < e0;
-				stk[sp] = swap ? c0 : c1;
-				stke[sp] = swap ? e0 : e1;
-				sp++;
-				node = swap ? c1 : c0;
-				descend = true;
-			} else if (h0) { node = c0; descend = true; }
-			else if (h1) { node = c1; descend = true; }
-		}
-		if (descend) continue;
-		bool done = false;
-		for (;;) {
-			if (sp == sp0) { done = true; break; }
-			sp--;
-			node = stk[sp];
-			const double lc = B.cut < RT_T_INF ? (B.cut * L.len) * (1.0 + 1e-9) + 1e-300 : RT_T_INF;
-			if (!(stke[sp] > lc)) break;
-		}
-		if (done) return;
-	}
-}
-
-// One collection pass over the scene-level tree (Scene::intersectList, scene.cpp:182-197).
-RT_HD void shadow_pass(const DScene& S, const d3& o, const d3& d, SBuf& B)
-{
-	int stk[RT_STACK];
-	double stke[RT_STACK];
-	const rt_node* nodes = S.snodes;
-	const d3 sl = slack_vec(d, S.scene_slack);
-	double e;
-	if (!box_hit(nodes[0].bmin, nodes[0].bmax, o, d, sl, e)) return;
-	int sp = 0, node = 0;
-	for (;;) {
-		const rt_node& n = nodes[node];
-		bool descend = false;
-		if (n.right < 0) {
-			for (int i = 0; i < n.count; i++) {
-				const int rank = n.first + i;
-				object_list(S, S.sitems[rank], (unsigned)rank, o, d, sl, B, stk, stke, sp);
-			}
-		} else {
-			const int c0 = node + 1, c1 = n.right;
-			double e0, e1;
-			bool h0 = box_hit(nodes[c0].bmin, nodes[c0].bmax, o, d, sl, e0) && !(e0 > B.cut);
-			bool h1 = box_hit(nodes[c1].bmin, nodes[c1].bmax, o, d, sl, e1) && !(e1 > B.cut);
-			if (h0 && h1) {
-				const bool swap = e1 < e0;
-				stk[sp] = swap ? c0 : c1;
-				stke[sp] = swap ? e0 : e1;
-				sp++;
-				node = swap ? c1 : c0;
-				descend = true;
-			} else if (h0) { node = c0; descend = true; }
-			else if (h1) { node = c1; descend = true; }
-		}
-		if (descend) continue;
-		bool done = false;
-		for (;;) {
-			if (sp == 0) { done = true; break; }
-			sp--;
-			node = stk[sp];
-			if (!(stke[sp] > B.cut)) break;
-		}
-		if (done) return;
-	}
-}
-
-// Light::srsAttenuation for point and directional lights (overlapping-objects mode off: the
-// medium outside every surface is `air`, kt = 1, transmissive; reference material.cpp:17-21).
-RT_HD d3 shadow_attenuation(const DScene& S, const rt_light& Lt, const d3& pos, const d3& dir, const rt_params& prm)
-{
-	const bool point = Lt.type != RT_LIGHT_DIRECTIONAL;
-	const d3 lpos = ld3(Lt.position);
-	double limit = RT_T_INF;
-	if (point) {
-		const double D = length(lpos - pos);
-		limit = D * (1.0 + 1e-9) + 1e-9;
-	}
-	d3 sattn = mk3(1.0, 1.0, 1.0);
-	double last_t = 0.0;
-	d3 cur = pos; // r2l position, advanced hit by hit (light.cpp:38)
-	const bool aterm = prm.aterm_thresh > 0.0;
-	SBuf B;
-	B.floor_t = -1.0;
-	B.floor_key = 0;
-	for (int pass = 0; pass < 1 << 20; pass++) {
-		B.n = 0;
-		B.cut = limit;
-		B.min_dropped = RT_T_INF;
-		shadow_pass(S, pos, dir, B);
-		const bool overflow = B.min_dropped < RT_T_INF && B.min_dropped <= B.cut;
-		for (int k = 0; k < B.n; k++) {
-			const SHit& h = B.h[k];
-			if (!(h.t <= B.cut)) break;
-			const double t = h.t - last_t;
-			last_t = h.t;
-			const bool inside = (h.flags & 1) != 0;
-			cur = cur + t * dir;
-			// curr/next media: inside ? (m_in -> air) : (air -> m_in)
-			if (point) { // PointLight::sattnLimitCheck (light.cpp:65-71)
-				if (dot(lpos - (cur + t * dir), dir) <= 0) return sattn;
-			}
-			const bool next_trans = inside ? true : (h.flags & 2) != 0;
-			if (!next_trans) return mk3(0.0, 0.0, 0.0);
-			if (aterm && dot(sattn, sattn) < prm.aterm_thresh * prm.aterm_thresh) return mk3(0.0, 0.0, 0.0);
-			const d3 kt = inside ? h.kt : mk3(1.0, 1.0, 1.0);
-			sattn = sattn * vpow(kt, t);
-			// once the attenuation is exactly 0 every later exit of the reference's loop returns 0
-			if (sattn.x == 0.0 && sattn.y == 0.0 && sattn.z == 0.0) return sattn;
-			B.floor_t = h.t;
-			B.floor_key = h.key;
-		}
-		if (!overflow && !(B.cut < limit)) return sattn; // the list is exhausted
-		if (!overflow) { // walked everything up to a cut that did not end the walk (delta == 0 case)
-			B.floor_t = B.cut;
-			B.floor_key = ~0ull;
-		}
-	}
-	return sattn;
-}
-
 } // namespace rtd

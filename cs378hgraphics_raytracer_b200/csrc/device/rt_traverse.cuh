@@ -1,0 +1,371 @@
+// rt_traverse.cuh - ONE tree-walk engine for both queries of the trace loop:
+//   closest hit  = Scene::intersect       (reference ray/src/scene/scene.cpp:157-180)
+//   all hits     = Scene::intersectList   (scene.cpp:182-197, feeding Light::srsAttenuation)
+// over the scene-level tree and, nested, the per-mesh trees (kdTree.h:100-117, scene.cpp:13-64,
+// SceneObjects/trimesh.cpp:79-105).
+//
+// The reference collects EVERY leaf item under boxes the ray touches, in DFS order, tests them all
+// and (closest hit) keeps the first candidate with a strictly smaller t, i.e. argmin of (t, rank).
+// Here each GPU thread walks front to back with a short stack, skips subtrees whose conservative
+// entry distance exceeds `lim` (the best t so far, or the shadow cut), and breaks ties in t by
+// candidate rank, so the winner is the reference's; box membership itself is decided by the
+// reference's exact slab arithmetic.  A trimesh is one scene-level candidate whose own winner is
+// chosen in object space by (t_local, leaf item position) - the reference's two-stage comparison.
+//
+// One loop serves both tree levels and both query kinds: a warp whose lanes hold a mix of camera,
+// secondary and shadow rays still executes the same box-test code together.  The loop has three
+// re-converging sections (while-while form): descend internal nodes / process one leaf / pop.
+#pragma once
+#include "rt_shadow.cuh"
+
+namespace rtd {
+
+enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1 };
+
+struct TravClosest {
+	bool have;
+	double best_t;
+	int best_rank, best_obj, best_fpos;
+};
+
+// world-space limit -> object space, inflated so rounding in the conversion can never cull a winner
+RT_HD double lim_to_local(double lim, double len) { return lim < RT_T_INF ? (lim * len) * (1.0 + 1e-9) + 1e-300 : RT_T_INF; }
+
+// emit one all-hits record of an analytic primitive (object space -> world)
+struct ListEmit {
+	const DScene& S;
+	const rt_object& ob;
+	const d3& dw;
+	double len;
+	unsigned rank;
+	SBuf& B;
+	RT_HD void operator()(double tl, d3 Nl, d2 uv, int sub) const
+	{
+		const double t = tl / len;
+		if (!(t <= B.cut)) return;
+		const rt_material& m = S.mats[ob.material];
+		const d3 N = world_normal(S, ob, Nl, uv);
+		sbuf_add(B, t, ((unsigned long long)rank << 32) | (unsigned)sub, dot(N, dw) > 0, m.trans != 0, mat_param(S, m, RT_KT, uv));
+	}
+};
+
+// all-hits record of a mesh face (TrimeshFace::intersectLocal's isect, trimesh.cpp:146-174)
+RT_HD void emit_face(const DScene& S, int obj, unsigned rank, int pos, double t, const d3& bary, const d3& dw, SBuf& B)
+{
+	const rt_object& ob = S.objs[obj];
+	const rt_mesh& M = S.meshes[ob.mesh];
+	Hit h;
+	h.obj = obj;
+	h.fpos = (int)M.item_off + pos;
+	h.face = S.mitems[h.fpos];
+	h.bary = bary;
+	h.uv.x = h.uv.y = 0.0;
+	const rt_face& f = S.faces[M.face_off + h.face];
+	d3 Nl;
+	if (M.vnorm_off >= 0) {
+		const double* n0 = S.vnormals + 3 * (M.vnorm_off + f.ids[0]);
+		const double* n1 = S.vnormals + 3 * (M.vnorm_off + f.ids[1]);
+		const double* n2 = S.vnormals + 3 * (M.vnorm_off + f.ids[2]);
+		Nl = normalize(mk3(n0[0] * bary.x + n1[0] * bary.y + n2[0] * bary.z,
+		                   n0[1] * bary.x + n1[1] * bary.y + n2[1] * bary.z,
+		                   n0[2] * bary.x + n1[2] * bary.y + n2[2] * bary.z));
+	} else {
+		Nl = ld3(f.normal);
+	}
+	const d3 N = normalize(mul33(ob.normi, Nl));
+	d3 kt;
+	bool trans;
+	eval_kt(S, h, kt, trans);
+	sbuf_add(B, t, ((unsigned long long)rank << 32) | (unsigned)pos, dot(N, dw) > 0, trans, kt);
+}
+
+template <bool PRUNE>
+RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode, TravClosest& C, SBuf& B)
+{
+	int stk[RT_STACK];
+	double stke[RT_STACK];
+	const bool prune = PRUNE || mode == TRAV_SHADOW;
+	// current space (world at level 0, the mesh's object space at level 1)
+	d3 o = ow, d = dw;
+	RayInv I = make_inv(d, prune ? S.scene_slack : 0.0);
+	const DNode2* nodes = S.snodes2;
+	int level = 0;
+	double lim = mode == TRAV_CLOSEST ? RT_T_INF : B.cut;
+	// mesh visit state
+	double len = 1.0;
+	int cur_obj = -1, cur_rank = 0, item_off = 0;
+	bool lhave = false;
+	double lbest_t = RT_T_INF;
+	int lbest_pos = 0x7fffffff;
+	const DTri* tris = S.tris;
+	double e;
+	if (!box_hit(S.stree.lo, S.stree.hi, o, d, I, e)) return;
+	int sp = 0;
+	int cur = S.stree.root;
+	for (;;) {
+		// ---- 1. internal nodes: test both children, go near, push far ---------------------------
+		while (cur >= 0) {
+			const DNode2& n = nodes[cur];
+			double e0, e1;
+			bool h0 = box_hit(n.lo0, n.hi0, o, d, I, e0);
+			bool h1 = box_hit(n.lo1, n.hi1, o, d, I, e1);
+			if (prune) { h0 = h0 && !(e0 > lim); h1 = h1 && !(e1 > lim); }
+			const int c0 = n.c0, c1 = n.c1;
+			if (h0 && h1) {
+				const bool swap = prune && e1 < e0;
+				stk[sp] = swap ? c0 : c1;
+				stke[sp] = swap ? e0 : e1;
+				sp++;
+				cur = swap ? c1 : c0;
+			} else if (h0) cur = c0;
+			else if (h1) cur = c1;
+			else cur = RT_REF_NONE;
+		}
+		// ---- 2. a leaf --------------------------------------------------------------------------
+		if (cur != RT_REF_NONE) {
+			const int first = leaf_first(cur), count = leaf_count(cur);
+			cur = RT_REF_NONE;
+			if (level == 1) {
+				for (int i = 0; i < count; i++) {
+					const int pos = first + i;
+					double t;
+					d3 bary;
+					if (mode == TRAV_CLOSEST) {
+						if (tri_hit<false>(tris[pos], o, d, t, bary)) {
+							if (!lhave || t < lbest_t || (t == lbest_t && pos < lbest_pos)) {
+								lhave = true;
+								lbest_t = t;
+								lbest_pos = pos;
+								if (t < lim) lim = t;
+							}
+						}
+					} else {
+						if (tri_hit<true>(tris[pos], o, d, t, bary)) {
+							const double tw = t / len;
+							if (tw <= B.cut) {
+								emit_face(S, cur_obj, (unsigned)cur_rank, pos, tw, bary, dw, B);
+								lim = lim_to_local(B.cut, len);
+							}
+						}
+					}
+				}
+			} else {
+				for (int i = 0; i < count; i++) {
+					const int rank = first + i;
+					const int obj = S.sitems[rank];
+					const rt_object& ob = S.objs[obj];
+					// Geometry::intersect / intersectList: world-bbox pretest (scene.cpp:15,43) is a real
+					// filter (leaf boxes are unions), then the object-space test
+					double eb;
+					if (!box_hit(ob.bbox, ob.bbox + 3, o, d, I, eb)) continue;
+					if (prune && eb > lim) continue;
+					const LocalRay L = to_local(ob, o, d);
+					if (ob.type == RT_OBJ_TRIMESH) {
+						// enter the mesh: remainder of this leaf, then the exit marker, then the mesh's nodes
+						if (i + 1 < count) { stk[sp] = leaf_ref(rank + 1, count - i - 1); stke[sp] = -RT_T_INF; sp++; }
+						stk[sp] = RT_REF_MESH_EXIT;
+						stke[sp] = -RT_T_INF;
+						sp++;
+						const DTree& T = S.mtrees[ob.mesh];
+						cur_obj = obj;
+						cur_rank = rank;
+						len = L.len;
+						item_off = (int)S.meshes[ob.mesh].item_off;
+						tris = S.tris + item_off;
+						nodes = S.mnodes2 + T.node_off;
+						o = L.o;
+						d = L.d;
+						I = make_inv(d, prune ? S.mesh_slack[ob.mesh] : 0.0);
+						level = 1;
+						lhave = false;
+						lbest_t = RT_T_INF;
+						lbest_pos = 0x7fffffff;
+						lim = lim_to_local(lim, len);
+						double er;
+						if (box_hit(T.lo, T.hi, o, d, I, er) && !(prune && er > lim)) cur = T.root;
+						break;
+					}
+					if (mode == TRAV_CLOSEST) {
+						LocalHit h;
+						int bf;
+						bool hit = false;
+						switch (ob.type) {
+						case RT_OBJ_SPHERE: hit = sphere_hit<false>(L.o, L.d, h); break;
+						case RT_OBJ_BOX: hit = box_prim_hit<false>(L.o, L.d, h, bf); break;
+						case RT_OBJ_SQUARE: hit = square_hit<false>(L.o, L.d, h); break;
+						case RT_OBJ_CYLINDER: hit = cylinder_hit<false>(L.o, L.d, h); break;
+						case RT_OBJ_CONE: hit = cone_hit<false>(L.o, L.d, ob.cone, ob.capped, h); break;
+						default: break;
+						}
+						if (hit) {
+							const double t = h.t / L.len;
+							if (!C.have || t < C.best_t || (t == C.best_t && rank < C.best_rank)) {
+								C.have = true;
+								C.best_t = t;
+								C.best_rank = rank;
+								C.best_obj = obj;
+								C.best_fpos = -1;
+								lim = t;
+							}
+						}
+					} else {
+						const ListEmit emit{S, ob, dw, L.len, (unsigned)rank, B};
+						switch (ob.type) {
+						case RT_OBJ_SPHERE: sphere_list(L.o, L.d, emit); break;
+						case RT_OBJ_BOX: box_list(L.o, L.d, emit); break;
+						case RT_OBJ_SQUARE: {
+							LocalHit h;
+							h.uv.x = h.uv.y = 0.0;
+							if (square_hit<true>(L.o, L.d, h)) emit(h.t, h.N, h.uv, 0);
+							break;
+						}
+						case RT_OBJ_CYLINDER: cylinder_list(L.o, L.d, emit); break;
+						case RT_OBJ_CONE: cone_list(L.o, L.d, ob.cone, ob.capped, emit); break;
+						default: break;
+						}
+						lim = B.cut;
+					}
+				}
+			}
+		}
+		// ---- 3. pop -----------------------------------------------------------------------------
+		if (cur == RT_REF_NONE) {
+			for (;;) {
+				if (sp == 0) return;
+				sp--;
+				const int a = stk[sp];
+				if (a == RT_REF_MESH_EXIT) {
+					// Trimesh::intersectLocal's winner goes back to the scene level as one candidate
+					if (mode == TRAV_CLOSEST && lhave) {
+						const double t = lbest_t / len;
+						if (!C.have || t < C.best_t || (t == C.best_t && cur_rank < C.best_rank)) {
+							C.have = true;
+							C.best_t = t;
+							C.best_rank = cur_rank;
+							C.best_obj = cur_obj;
+							C.best_fpos = item_off + lbest_pos;
+						}
+					}
+					o = ow;
+					d = dw;
+					I = make_inv(d, prune ? S.scene_slack : 0.0);
+					nodes = S.snodes2;
+					level = 0;
+					lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : B.cut;
+					continue;
+				}
+				if (prune && stke[sp] > lim) continue;
+				cur = a;
+				break;
+			}
+		}
+	}
+}
+
+// Scene::intersect.  On return out.obj/out.fpos/out.t identify the winner; finalize_hit fills the rest.
+template <bool PRUNE> RT_HD bool closest_hit(const DScene& S, const d3& o, const d3& d, Hit& out)
+{
+	TravClosest C;
+	C.have = false;
+	C.best_t = RT_T_INF;
+	C.best_rank = 0x7fffffff;
+	C.best_obj = -1;
+	C.best_fpos = -1;
+	SBuf unused;
+	unused.n = 0;
+	unused.cut = RT_T_INF;
+	traverse<PRUNE>(S, o, d, TRAV_CLOSEST, C, unused);
+	out.obj = -1;
+	out.face = -1;
+	out.fpos = -1;
+	out.t = 1000.0; // scene.cpp:174-175
+	if (!C.have) return false;
+	out.obj = C.best_obj;
+	out.fpos = C.best_fpos;
+	out.t = C.best_t;
+	return true;
+}
+
+
+// ---- Light::srsAttenuation's walk over the sorted hits (reference scene/light.cpp:28-52) --------
+struct ShadowState {
+	d3 sattn;    // running attenuation
+	d3 cur;      // r2l position, advanced hit by hit (light.cpp:38)
+	double last_t;
+	double limit; // hits beyond this cannot change the result (past a point light)
+	int point;
+};
+
+RT_HD void shadow_begin(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& pos)
+{
+	st.point = Lt.type != RT_LIGHT_DIRECTIONAL;
+	st.limit = RT_T_INF;
+	if (st.point) {
+		const double D = length(ld3(Lt.position) - pos);
+		st.limit = D * (1.0 + 1e-9) + 1e-9;
+	}
+	st.sattn = mk3(1.0, 1.0, 1.0);
+	st.last_t = 0.0;
+	st.cur = pos;
+	B.floor_t = -1.0;
+	B.floor_key = 0;
+}
+RT_HD void shadow_pass_reset(const ShadowState& st, SBuf& B)
+{
+	B.n = 0;
+	B.cut = st.limit;
+	B.min_dropped = RT_T_INF;
+}
+// Consumes one collection pass.  Returns true when the attenuation is final (in st.sattn); false
+// when another pass (continuing after B.floor) is needed.
+RT_HD bool shadow_walk(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& dir, const rt_params& prm)
+{
+	const bool overflow = B.min_dropped < RT_T_INF && B.min_dropped <= B.cut;
+	const bool aterm = prm.aterm_thresh > 0.0;
+	const d3 lpos = ld3(Lt.position);
+	for (int k = 0; k < B.n; k++) {
+		const SHit& h = B.h[k];
+		if (!(h.t <= B.cut)) break;
+		const double t = h.t - st.last_t;
+		st.last_t = h.t;
+		const bool inside = (h.flags & 1) != 0;
+		st.cur = st.cur + t * dir;
+		// curr/next media: inside ? (m_in -> air) : (air -> m_in); overlapping-objects mode off
+		if (st.point) { // PointLight::sattnLimitCheck (light.cpp:65-71)
+			if (dot(lpos - (st.cur + t * dir), dir) <= 0) return true;
+		}
+		const bool next_trans = inside ? true : (h.flags & 2) != 0;
+		if (!next_trans) { st.sattn = mk3(0.0, 0.0, 0.0); return true; }
+		if (aterm && dot(st.sattn, st.sattn) < prm.aterm_thresh * prm.aterm_thresh) { st.sattn = mk3(0.0, 0.0, 0.0); return true; }
+		const d3 kt = inside ? h.kt : mk3(1.0, 1.0, 1.0);
+		st.sattn = st.sattn * vpow(kt, t);
+		// once the attenuation is exactly 0 every later exit of the reference's loop returns 0
+		if (st.sattn.x == 0.0 && st.sattn.y == 0.0 && st.sattn.z == 0.0) return true;
+		B.floor_t = h.t;
+		B.floor_key = h.key;
+	}
+	if (!overflow && !(B.cut < st.limit)) return true; // the list is exhausted
+	if (!overflow) { // walked everything up to a cut that did not end the walk (delta == 0 case)
+		B.floor_t = B.cut;
+		B.floor_key = ~0ull;
+	}
+	return false;
+}
+
+// Light::srsAttenuation for point and directional lights
+RT_HD d3 shadow_attenuation(const DScene& S, const rt_light& Lt, const d3& pos, const d3& dir, const rt_params& prm)
+{
+	ShadowState st;
+	SBuf B;
+	TravClosest unused;
+	unused.have = false;
+	shadow_begin(st, B, Lt, pos);
+	for (int pass = 0; pass < 1 << 20; pass++) {
+		shadow_pass_reset(st, B);
+		traverse<true>(S, pos, dir, TRAV_SHADOW, unused, B);
+		if (shadow_walk(st, B, Lt, dir, prm)) break;
+	}
+	return st.sattn;
+}
+
+} // namespace rtd

@@ -91,7 +91,8 @@ rt_status launch_pool(rt_ctx* ctx, PoolArgs& A)
 {
 	const int warps_per_block = RT_POOL_THREADS / 32;
 	const long long warps = (long long)ctx->pool_blocks * warps_per_block;
-	A.cap = 32 * (A.depth + 3);
+	const bool defer = !(A.prm.aterm_thresh > 0.0);
+	A.cap = 32 * (A.depth + 3) + (defer ? 64 * ctx->S.n_lights + 64 : 0);
 	rt_status st;
 	if ((st = ensure(ctx, B_POOL_D, (size_t)warps * A.cap * RT_POOL_DOUBLES * sizeof(double))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_POOL_I, (size_t)warps * A.cap * 2 * sizeof(int))) != RT_OK) return st;
@@ -102,7 +103,8 @@ rt_status launch_pool(rt_ctx* ctx, PoolArgs& A)
 	A.stats = small;
 	CK(cudaMemsetAsync(A.cursor, 0, sizeof(unsigned long long), ctx->stream));
 	if (A.n_slots > 0) {
-		k_trace_pool<<<ctx->pool_blocks, RT_POOL_THREADS, 0, ctx->stream>>>(ctx->S, A);
+		if (defer) k_trace_pool<true><<<ctx->pool_blocks, RT_POOL_THREADS, 0, ctx->stream>>>(ctx->S, A);
+		else k_trace_pool<false><<<ctx->pool_blocks, RT_POOL_THREADS, 0, ctx->stream>>>(ctx->S, A);
 		ctx->launches++;
 		CK(cudaGetLastError());
 	}
@@ -147,7 +149,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	cudaEventCreate(&ctx->ev1);
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_pool, RT_POOL_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_pool<true>, RT_POOL_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
 	ctx->pool_blocks = per_sm * ctx->sm_count;
 	if (cudaMalloc(&ctx->buf[B_SMALL], 256) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	ctx->buf_bytes[B_SMALL] = 256;
@@ -186,13 +188,16 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 		}
 	Derived D;
 	derive(A, D);
-	if (D.max_scene_depth + D.max_mesh_depth > RT_STACK - 2) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
+	if (D.max_scene_depth + D.max_mesh_depth > RT_STACK - 4 || A.count(RT_SEC_MESH_ITEMS) >= (1ull << 29) || A.count(RT_SEC_SCENE_ITEMS) >= (1ull << 29)) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
 	free_scene(ctx);
 	DScene& S = ctx->S;
 	std::memset(&S, 0, sizeof(S));
 	rt_status st;
 #define UP(field, type, sec)                                                                        \
 	if ((st = upload<type>(ctx, A.ptr<type>(sec), A.count(sec), &S.field)) != RT_OK) { free_scene(ctx); return st; }
+	if ((st = upload<DNode2>(ctx, D.snodes2.data(), D.snodes2.size(), &S.snodes2)) != RT_OK) { free_scene(ctx); return st; }
+	if ((st = upload<DNode2>(ctx, D.mnodes2.data(), D.mnodes2.size(), &S.mnodes2)) != RT_OK) { free_scene(ctx); return st; }
+	if ((st = upload<DTree>(ctx, D.mtrees.data(), D.mtrees.size(), &S.mtrees)) != RT_OK) { free_scene(ctx); return st; }
 	UP(snodes, rt_node, RT_SEC_SCENE_NODES)
 	UP(sitems, int32_t, RT_SEC_SCENE_ITEMS)
 	UP(objs, rt_object, RT_SEC_OBJECTS)
@@ -213,6 +218,7 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	S.cam = *A.ptr<rt_camera>(RT_SEC_CAMERA);
 	S.glob = *A.ptr<rt_globals>(RT_SEC_GLOBALS);
 	S.scene_slack = D.scene_slack;
+	S.stree = D.stree;
 	S.n_lights = (int)A.count(RT_SEC_LIGHTS);
 	S.n_objs = (int)A.count(RT_SEC_OBJECTS);
 	CK(cudaStreamSynchronize(ctx->stream)); // D's host vectors die with this scope
@@ -457,6 +463,20 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
 		CK(cudaMemcpyAsync(rgb_out, A.accum, (size_t)n * 24, cudaMemcpyDeviceToHost, ctx->stream));
 	}
 	return read_stats(ctx, nullptr, 0.f);
+}
+
+
+rt_status rt_selftest_division(rt_ctx* ctx, long long n, unsigned long long seed, int exp_range, unsigned long long* mismatches)
+{
+	if (!ctx || !mismatches || n <= 0 || exp_range < 0 || exp_range > 250) return RT_ERR_ARG;
+	CK(cudaSetDevice(ctx->device));
+	unsigned long long* cnt = (unsigned long long*)ctx->buf[B_SMALL] + 24;
+	CK(cudaMemsetAsync(cnt, 0, 8, ctx->stream));
+	k_div_selftest<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(seed, n, exp_range, cnt);
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(mismatches, cnt, 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return RT_OK;
 }
 
 } // extern "C"

@@ -120,6 +120,11 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int n, int depth,
                         rt_hit* hits_out, double* rgb_out);
 
+/* Device self-test: n pseudo-random quotients a/d computed by the slab test's FMA-corrected
+ * reciprocal division (device/rt_math.cuh div_by) are compared bit for bit with IEEE division;
+ * exponents of a and d are drawn from [-exp_range, exp_range].  *mismatches must come back 0. */
+rt_status rt_selftest_division(rt_ctx* ctx, long long n, unsigned long long seed, int exp_range, unsigned long long* mismatches);
+
 /* ---- host-side scene loading (no GPU needed) -------------------------------------------- */
 /* Replaces Tokenizer + Parser::parseScene + Scene::add/conclude + Trimesh::conclude (reference
  * parser/Parser.cpp:26-95, scene.cpp:133-153, trimesh.cpp:69-77, kdTree.h:23-78): parses a .ray

@@ -23,6 +23,10 @@ void setup(Sim& sim, const void* arena)
 	rt::ArenaView A(arena);
 	derive(A, sim.D);
 	DScene& S = sim.S;
+	S.snodes2 = sim.D.snodes2.data();
+	S.stree = sim.D.stree;
+	S.mnodes2 = sim.D.mnodes2.data();
+	S.mtrees = sim.D.mtrees.data();
 	S.snodes = A.ptr<rt_node>(RT_SEC_SCENE_NODES);
 	S.sitems = A.ptr<int32_t>(RT_SEC_SCENE_ITEMS);
 	S.objs = A.ptr<rt_object>(RT_SEC_OBJECTS);

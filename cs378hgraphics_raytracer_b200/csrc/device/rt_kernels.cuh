@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(256) k_div_selftest(unsigned long long seed, l
 	const double a = __longlong_as_double(sa | ((unsigned long long)(1023 + ea) << 52) | (ma & 0xfffffffffffffull));
 	const double d = __longlong_as_double(sd | ((unsigned long long)(1023 + ed) << 52) | (md & 0xfffffffffffffull));
 	const double y = 1.0 / d;
-	const double q1 = div_by(a, d, y), q2 = a / d;
+	const double q1 = div_by(a, d, y, div_range_ok(d) ? 1201u : 0u), q2 = a / d;
 	if (__double_as_longlong(q1) != __double_as_longlong(q2)) atomicAdd(mismatches, 1ull);
 }
 } // namespace rtd

@@ -14,7 +14,7 @@ RT_HD d3 tex_pixel(const DScene& S, const rt_texture& T, int x, int y)
 	}
 	return mk3(0.0, 0.0, 0.0);
 }
-RT_HD d3 tex_sample(const DScene& S, int tex, d2 uv)
+RT_COLD d3 tex_sample(const DScene& S, int tex, d2 uv)
 {
 	const rt_texture T = S.texs[tex];
 	double x = uv.x, y = uv.y;
@@ -66,7 +66,7 @@ RT_HD d3 blend3(const double* a, const double* b, const double* c, d3 w)
 }
 
 // kt only (shadow rays need nothing else)
-RT_HD void eval_kt(const DScene& S, const Hit& h, d3& kt, bool& trans)
+RT_COLD void eval_kt(const DScene& S, const Hit& h, d3& kt, bool& trans)
 {
 	const int vb = mesh_vmat_base(S, h);
 	if (vb >= 0) {
@@ -83,7 +83,7 @@ RT_HD void eval_kt(const DScene& S, const Hit& h, d3& kt, bool& trans)
 	trans = m.trans != 0;
 }
 
-RT_HD void eval_material(const DScene& S, const Hit& h, MatEval& e)
+RT_COLD void eval_material(const DScene& S, const Hit& h, MatEval& e)
 {
 	const int vb = mesh_vmat_base(S, h);
 	if (vb >= 0) {
@@ -121,7 +121,7 @@ RT_HD void eval_material(const DScene& S, const Hit& h, MatEval& e)
 
 // Object-space normal of an analytic hit -> world (TransformNode::localToGlobalCoordsNormal,
 // reference scene.h:108-111), including Box::computeNormal's bump map (Box.cpp:99-108).
-RT_HD d3 world_normal(const DScene& S, const rt_object& ob, d3 Nl, d2 uv)
+RT_COLD d3 world_normal(const DScene& S, const rt_object& ob, d3 Nl, d2 uv)
 {
 	if (ob.type == RT_OBJ_BOX) {
 		const rt_material& m = S.mats[ob.material];
@@ -133,10 +133,11 @@ RT_HD d3 world_normal(const DScene& S, const rt_object& ob, d3 Nl, d2 uv)
 
 // Re-runs the winning primitive's test in its full form to obtain N, uv, barycentrics - the
 // traversal itself only carries (t, object, leaf item).  Same arithmetic, same t.
-RT_HD void finalize_hit(const DScene& S, const d3& o, const d3& d, Hit& h)
+RT_COLD void finalize_hit(const DScene& S, const d3& o, const d3& d, Hit& h)
 {
 	const rt_object& ob = S.objs[h.obj];
-	const LocalRay L = to_local(ob, o, d);
+	LocalRay L;
+	to_local(L, ob, o, d);
 	LocalHit lh;
 	lh.uv.x = lh.uv.y = 0.0; // isect() zero-initialises uvCoordinates (glm 0.9.8 default ctor)
 	lh.N = mk3(0, 0, 0);

@@ -12,6 +12,7 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 
 #ifdef __CUDACC__
 #define RT_HD __host__ __device__ __forceinline__
@@ -19,6 +20,14 @@
 #else
 #define RT_HD inline
 #define RT_HDN inline
+#endif
+// RT_COLD: code outside the box/triangle loop.  The trace kernel is instruction-fetch bound when
+// everything is inlined (profiles/r1_v2_*: 47k SASS instructions, 52-80% stall_no_inst), so the
+// rarely executed parts are real calls and the tree-walk loop stays within the 32 KB L1.5 I-cache.
+#if defined(__CUDACC__) && !defined(RT_INLINE_ALL)
+#define RT_COLD __host__ __device__ __noinline__
+#else
+#define RT_COLD RT_HD
 #endif
 
 namespace rtd {
@@ -41,8 +50,12 @@ RT_HD d3 operator-(d3 a) { return mk3(-a.x, -a.y, -a.z); }
 RT_HD double comp(const d3& v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : v.z); }
 
 RT_HD double dot(d3 a, d3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
-RT_HD double length(d3 a) { return sqrt(dot(a, a)); }
-RT_HD d3 normalize(d3 a) { return a * (1.0 / sqrt(dot(a, a))); }
+// one copy each of the IEEE sqrt / division expansions (~50 SASS instructions apiece)
+RT_COLD double dsqrt(double x) { return sqrt(x); }
+RT_COLD double inv_sqrt(double x) { return 1.0 / sqrt(x); }
+RT_COLD double ddiv(double a, double b) { return a / b; }
+RT_HD double length(d3 a) { return dsqrt(dot(a, a)); }
+RT_HD d3 normalize(d3 a) { return a * inv_sqrt(dot(a, a)); }
 RT_HD d3 cross(d3 a, d3 b) { return mk3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
 RT_HD double gmin(double x, double y) { return (y < x) ? y : x; }
 RT_HD double gmax(double x, double y) { return (x < y) ? y : x; }
@@ -76,23 +89,34 @@ RT_HD d3 mul33(const double* m, d3 v)
 // real division runs.  tests/test_gpu_parity.py::test_division_selftest compares 2^28 quotients
 // against the hardware sequence bit for bit.
 struct RayInv {
-	d3 y;    // 1/d per axis (IEEE)
-	d3 sl;   // pruning slack per axis = slack/|d|
-	bool slow; // some |d| outside [2^-300, 2^300]: use real divisions
+	d3 y;          // 1/d per axis (IEEE)
+	d3 sl;         // pruning slack per axis = slack/|d|
+	unsigned span; // width of the exponent window of `a` served by the FMA path: 1201, or 0 when
+	               // some |d| lies outside [2^-300, 2^300] (every quotient is then a real division)
 };
 RT_HD bool div_range_ok(double d) { const double a = fabs(d); return d == 0.0 || (a >= 0x1p-300 && a <= 0x1p300); }
-RT_HD RayInv make_inv(const d3& d, double slack)
+RT_COLD void make_inv(RayInv& I, const d3& d, double slack)
 {
-	RayInv I;
 	I.y = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
 	I.sl = mk3(slack * fabs(I.y.x), slack * fabs(I.y.y), slack * fabs(I.y.z));
-	I.slow = !(div_range_ok(d.x) && div_range_ok(d.y) && div_range_ok(d.z));
-	return I;
+	I.span = (div_range_ok(d.x) && div_range_ok(d.y) && div_range_ok(d.z)) ? 1201u : 0u;
 }
-RT_HD double div_by(double a, double d, double y)
+RT_HD unsigned biased_exp(double a)
 {
-	const double m = fabs(a);
-	if (!(m <= 0x1p600) || (m < 0x1p-600 && a != 0.0)) return a / d;
+#ifdef __CUDA_ARCH__
+	return ((unsigned)__double2hiint(a) >> 20) & 0x7ffu;
+#else
+	uint64_t u;
+	memcpy(&u, &a, 8);
+	return (unsigned)(u >> 52) & 0x7ffu;
+#endif
+}
+RT_HD double div_by(double a, double d, double y, unsigned span)
+{
+	// FMA path for 2^-600 <= |a| < 2^601 (biased exponent 423..1623) and for a == 0
+	if (biased_exp(a) - 423u >= span) {
+		if (span == 0u || a != 0.0) return ddiv(a, d);
+	}
 	double q = a * y;
 	double r = fma(-q, d, a);
 	q = fma(r, y, q);

@@ -68,7 +68,7 @@ __device__ __forceinline__ void accumulate(double* accum, int sample, const d3& 
 // DEFER = false: shadow rays traced inline by the shading lane (adaptive termination needs the
 //                shadowed colour before deciding to recurse, RayTracer.cpp:124-125)
 template <bool DEFER>
-__global__ void __launch_bounds__(RT_POOL_THREADS, RT_POOL_MINB) k_trace_pool(const DScene S, const PoolArgs A)
+__global__ void __launch_bounds__(RT_POOL_THREADS, RT_POOL_MINB) k_trace_pool(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A)
 {
 	const unsigned lane = threadIdx.x & 31;
 	const unsigned lt_mask = (1u << lane) - 1u;

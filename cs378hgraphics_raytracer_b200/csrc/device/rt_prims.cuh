@@ -16,9 +16,8 @@ RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3
 	double tMin = -1.0e308, tMax = 1.0e308, en = -1.0e308;
 #define RT_SLAB(O, D, Y, LO, HI, SL)                                        \
 	if (D != 0.0) {                                                         \
-		double t1, t2;                                                      \
-		if (I.slow) { t1 = (LO - O) / D; t2 = (HI - O) / D; }               \
-		else { t1 = div_by(LO - O, D, Y); t2 = div_by(HI - O, D, Y); }      \
+		double t1 = div_by(LO - O, D, Y, I.span);                           \
+		double t2 = div_by(HI - O, D, Y, I.span);                           \
 		if (t1 > t2) { double tt = t1; t1 = t2; t2 = tt; }                  \
 		if (t1 > tMin) tMin = t1;                                           \
 		if (t2 < tMax) tMax = t2;                                           \

@@ -16,7 +16,7 @@ RT_HD void camera_ray(const rt_camera& C, double x, double y, d3& o, d3& d)
 // The `lens`-th ray RayTracer::trace shoots for window point (x,y): lens 0 is the pinhole ray,
 // lens 1..divs are the depth-of-field rays (reference RayTracer.cpp:35-79).  eye_shift moves the
 // eye along +x (anaglyph second eye, RayTracer.cpp:92-99).
-RT_HD void primary_ray(const rt_camera& C, const rt_params& prm, double x, double y, int lens, double eye_shift, d3& o, d3& d)
+RT_COLD void primary_ray(const rt_camera& C, const rt_params& prm, double x, double y, int lens, double eye_shift, d3& o, d3& d)
 {
 	camera_ray(C, x, y, o, d);
 	if (eye_shift != 0.0) o = ld3(C.eye) + mk3(eye_shift, 0.0, 0.0);
@@ -44,7 +44,7 @@ RT_HD void primary_ray(const rt_camera& C, const rt_params& prm, double x, doubl
 // DirectionalLight (scene/light.cpp:56-73): everything except the shadow attenuation, plus the
 // shadow ray Light::shadowAttenuation would trace (light.cpp:16-20: origin backed up along the
 // view ray by 1e-10, aimed at the light).  term = (dattn * Lc) * (d_comp + s_comp).
-RT_HD void light_term(const rt_light& L, const MatEval& m, const d3& P, const d3& N, const d3& view, d3& term, d3& pb, d3& sdir)
+RT_COLD void light_term(const rt_light& L, const MatEval& m, const d3& P, const d3& N, const d3& view, d3& term, d3& pb, d3& sdir)
 {
 	const bool point = L.type != RT_LIGHT_DIRECTIONAL;
 	const d3 lpos = ld3(L.position);
@@ -95,7 +95,7 @@ struct RayTask {
 
 // CubeMap::getColor (reference scene/cubeMap.cpp:12-44) for a ray that hit nothing; ties leave
 // map/d unset in the reference (UB), pinned by the oracle build to map 0, d = 0.
-RT_HD d3 miss_colour(const DScene& S, const rt_params& prm, const d3& rd)
+RT_COLD d3 miss_colour(const DScene& S, const rt_params& prm, const d3& rd)
 {
 	if (!(prm.use_cubemap && S.glob.has_cubemap)) return mk3(0.0, 0.0, 0.0);
 	const double ax = fabs(rd.x), ay = fabs(rd.y), az = fabs(rd.z);
@@ -112,7 +112,7 @@ RT_HD d3 miss_colour(const DScene& S, const rt_params& prm, const d3& rd)
 }
 
 // weight of a ray once its own hit distance is known (RayTracer.cpp:149,162)
-RT_HD d3 apply_att(const d3& w, const d3& att_kt, int att_mode, double t)
+RT_COLD d3 apply_att(const d3& w, const d3& att_kt, int att_mode, double t)
 {
 	if (att_mode == 1) return w * gclamp(vpow(att_kt, t), 0.0, 1.0);
 	if (att_mode == 2) return w * vpow(att_kt, t);
@@ -123,7 +123,7 @@ RT_HD d3 apply_att(const d3& w, const d3& att_kt, int att_mode, double t)
 // hit of ray (ro, rd) with weight w; depth is the already decremented depth.  Overlapping-objects
 // mode is off: the medium on the far side of a surface is air (index 1, kt 1; material.cpp:17-21).
 // kid[0] = reflection (valid if has_refl), kid[1] = refraction (valid if has_refr).
-RT_HD void spawn_children(const MatEval& m, const Hit& h, const d3& ro, const d3& rd, const d3& w, int depth, RayTask* kid, bool& has_refl, bool& has_refr)
+RT_COLD void spawn_children(const MatEval& m, const Hit& h, const d3& ro, const d3& rd, const d3& w, int depth, RayTask* kid, bool& has_refl, bool& has_refr)
 {
 	has_refl = has_refr = false;
 	if (!(m.recur && depth > 0)) return;

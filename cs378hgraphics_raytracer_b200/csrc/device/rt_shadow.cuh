@@ -40,7 +40,7 @@ struct SBuf {
 
 RT_HD bool key_less(double ta, unsigned long long ka, double tb, unsigned long long kb) { return ta < tb || (ta == tb && ka < kb); }
 
-RT_HD void sbuf_add(SBuf& B, double t, unsigned long long key, bool inside, bool trans, const d3& kt)
+RT_COLD void sbuf_add(SBuf& B, double t, unsigned long long key, bool inside, bool trans, const d3& kt)
 {
 	if (!(t <= B.cut)) return;
 	if (!key_less(B.floor_t, B.floor_key, t, key)) return;

@@ -35,14 +35,12 @@ struct LocalRay {
 };
 
 // Geometry::intersect's world -> object ray (reference scene.cpp:17-20)
-RT_HD LocalRay to_local(const rt_object& ob, const d3& o, const d3& d)
+RT_COLD void to_local(LocalRay& L, const rt_object& ob, const d3& o, const d3& d)
 {
-	LocalRay L;
 	L.o = xform_point(ob.inv, o);
 	d3 dir = xform_point(ob.inv, o + d) - L.o;
 	L.len = length(dir);
 	L.d = normalize(dir);
-	return L;
 }
 
 // TrimeshFace::intersectLocal (reference SceneObjects/trimesh.cpp:119-188): plane, three edge

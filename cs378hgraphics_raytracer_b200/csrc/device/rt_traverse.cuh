@@ -49,8 +49,55 @@ struct ListEmit {
 	}
 };
 
-// all-hits record of a mesh face (TrimeshFace::intersectLocal's isect, trimesh.cpp:146-174)
-RT_HD void emit_face(const DScene& S, int obj, unsigned rank, int pos, double t, const d3& bary, const d3& dw, SBuf& B)
+// Scene-level candidate that is an analytic primitive, closest-hit query: the object-space test
+// and the (t, rank) comparison of Scene::intersect's loop (scene.cpp:163-172).
+RT_COLD void prim_closest(const rt_object& ob, const LocalRay& L, int rank, int obj, TravClosest& C)
+{
+	LocalHit h;
+	int bf;
+	bool hit = false;
+	switch (ob.type) {
+	case RT_OBJ_SPHERE: hit = sphere_hit<false>(L.o, L.d, h); break;
+	case RT_OBJ_BOX: hit = box_prim_hit<false>(L.o, L.d, h, bf); break;
+	case RT_OBJ_SQUARE: hit = square_hit<false>(L.o, L.d, h); break;
+	case RT_OBJ_CYLINDER: hit = cylinder_hit<false>(L.o, L.d, h); break;
+	case RT_OBJ_CONE: hit = cone_hit<false>(L.o, L.d, ob.cone, ob.capped, h); break;
+	default: break;
+	}
+	if (!hit) return;
+	const double t = h.t / L.len;
+	if (!C.have || t < C.best_t || (t == C.best_t && rank < C.best_rank)) {
+		C.have = true;
+		C.best_t = t;
+		C.best_rank = rank;
+		C.best_obj = obj;
+		C.best_fpos = -1;
+	}
+}
+
+// The same candidate for the all-hits query (Geometry::intersectList, scene.cpp:41-64)
+RT_COLD void prim_list(const DScene& S, const rt_object& ob, const LocalRay& L, const d3& dw, int rank, SBuf& B)
+{
+	const ListEmit emit{S, ob, dw, L.len, (unsigned)rank, B};
+	switch (ob.type) {
+	case RT_OBJ_SPHERE: sphere_list(L.o, L.d, emit); break;
+	case RT_OBJ_BOX: box_list(L.o, L.d, emit); break;
+	case RT_OBJ_SQUARE: {
+		LocalHit h;
+		h.uv.x = h.uv.y = 0.0;
+		if (square_hit<true>(L.o, L.d, h)) emit(h.t, h.N, h.uv, 0);
+		break;
+	}
+	case RT_OBJ_CYLINDER: cylinder_list(L.o, L.d, emit); break;
+	case RT_OBJ_CONE: cone_list(L.o, L.d, ob.cone, ob.capped, emit); break;
+	default: break;
+	}
+}
+
+// all-hits record of a mesh face (TrimeshFace::intersectLocal's isect, trimesh.cpp:146-174).
+// The walk found the hit with the short form of the triangle test; the full form is re-run here
+// for the barycentrics (same arithmetic, same t).
+RT_COLD void emit_face(const DScene& S, int obj, unsigned rank, int pos, double len, const d3& o, const d3& d, const d3& dw, SBuf& B)
 {
 	const rt_object& ob = S.objs[obj];
 	const rt_mesh& M = S.meshes[ob.mesh];
@@ -58,17 +105,20 @@ RT_HD void emit_face(const DScene& S, int obj, unsigned rank, int pos, double t,
 	h.obj = obj;
 	h.fpos = (int)M.item_off + pos;
 	h.face = S.mitems[h.fpos];
-	h.bary = bary;
 	h.uv.x = h.uv.y = 0.0;
+	double tl;
+	tri_hit<true>(S.tris[h.fpos], o, d, tl, h.bary);
+	const double t = tl / len;
+	if (!(t <= B.cut)) return;
 	const rt_face& f = S.faces[M.face_off + h.face];
 	d3 Nl;
 	if (M.vnorm_off >= 0) {
 		const double* n0 = S.vnormals + 3 * (M.vnorm_off + f.ids[0]);
 		const double* n1 = S.vnormals + 3 * (M.vnorm_off + f.ids[1]);
 		const double* n2 = S.vnormals + 3 * (M.vnorm_off + f.ids[2]);
-		Nl = normalize(mk3(n0[0] * bary.x + n1[0] * bary.y + n2[0] * bary.z,
-		                   n0[1] * bary.x + n1[1] * bary.y + n2[1] * bary.z,
-		                   n0[2] * bary.x + n1[2] * bary.y + n2[2] * bary.z));
+		Nl = normalize(mk3(n0[0] * h.bary.x + n1[0] * h.bary.y + n2[0] * h.bary.z,
+		                   n0[1] * h.bary.x + n1[1] * h.bary.y + n2[1] * h.bary.z,
+		                   n0[2] * h.bary.x + n1[2] * h.bary.y + n2[2] * h.bary.z));
 	} else {
 		Nl = ld3(f.normal);
 	}
@@ -79,6 +129,17 @@ RT_HD void emit_face(const DScene& S, int obj, unsigned rank, int pos, double t,
 	sbuf_add(B, t, ((unsigned long long)rank << 32) | (unsigned)pos, dot(N, dw) > 0, trans, kt);
 }
 
+// State of a walk that is inside a mesh (level 1); kept in one struct so that the cold
+// enter/leave code can live in real functions.
+struct MeshVisit {
+	double len;      // |M^-1 d|: t_world = t_local / len
+	int obj, rank;   // the scene-level candidate being visited
+	int item_off;    // first leaf item of this mesh in tris[] / mitems[]
+	bool have;       // Trimesh::intersectLocal's running winner (object space)
+	double best_t;
+	int best_pos;
+};
+
 template <bool PRUNE>
 RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode, TravClosest& C, SBuf& B)
 {
@@ -87,23 +148,27 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode,
 	const bool prune = PRUNE || mode == TRAV_SHADOW;
 	// current space (world at level 0, the mesh's object space at level 1)
 	d3 o = ow, d = dw;
-	RayInv I = make_inv(d, prune ? S.scene_slack : 0.0);
+	RayInv I;
+	make_inv(I, d, prune ? S.scene_slack : 0.0);
 	const DNode2* nodes = S.snodes2;
+	const DTri* tris = S.tris;
 	int level = 0;
 	double lim = mode == TRAV_CLOSEST ? RT_T_INF : B.cut;
-	// mesh visit state
-	double len = 1.0;
-	int cur_obj = -1, cur_rank = 0, item_off = 0;
-	bool lhave = false;
-	double lbest_t = RT_T_INF;
-	int lbest_pos = 0x7fffffff;
-	const DTri* tris = S.tris;
+	MeshVisit V;
+	V.len = 1.0;
+	V.obj = -1;
+	V.rank = 0;
+	V.item_off = 0;
+	V.have = false;
+	V.best_t = RT_T_INF;
+	V.best_pos = 0x7fffffff;
 	double e;
 	if (!box_hit(S.stree.lo, S.stree.hi, o, d, I, e)) return;
 	int sp = 0;
 	int cur = S.stree.root;
 	for (;;) {
 		// ---- 1. internal nodes: test both children, go near, push far ---------------------------
+#pragma unroll 1
 		while (cur >= 0) {
 			const DNode2& n = nodes[cur];
 			double e0, e1;
@@ -126,30 +191,26 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode,
 			const int first = leaf_first(cur), count = leaf_count(cur);
 			cur = RT_REF_NONE;
 			if (level == 1) {
+#pragma unroll 1
 				for (int i = 0; i < count; i++) {
 					const int pos = first + i;
 					double t;
 					d3 bary;
+					if (!tri_hit<false>(tris[pos], o, d, t, bary)) continue;
 					if (mode == TRAV_CLOSEST) {
-						if (tri_hit<false>(tris[pos], o, d, t, bary)) {
-							if (!lhave || t < lbest_t || (t == lbest_t && pos < lbest_pos)) {
-								lhave = true;
-								lbest_t = t;
-								lbest_pos = pos;
-								if (t < lim) lim = t;
-							}
+						if (!V.have || t < V.best_t || (t == V.best_t && pos < V.best_pos)) {
+							V.have = true;
+							V.best_t = t;
+							V.best_pos = pos;
+							if (t < lim) lim = t;
 						}
 					} else {
-						if (tri_hit<true>(tris[pos], o, d, t, bary)) {
-							const double tw = t / len;
-							if (tw <= B.cut) {
-								emit_face(S, cur_obj, (unsigned)cur_rank, pos, tw, bary, dw, B);
-								lim = lim_to_local(B.cut, len);
-							}
-						}
+						emit_face(S, V.obj, (unsigned)V.rank, pos, V.len, o, d, dw, B);
+						lim = lim_to_local(B.cut, V.len);
 					}
 				}
 			} else {
+#pragma unroll 1
 				for (int i = 0; i < count; i++) {
 					const int rank = first + i;
 					const int obj = S.sitems[rank];
@@ -159,7 +220,8 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode,
 					double eb;
 					if (!box_hit(ob.bbox, ob.bbox + 3, o, d, I, eb)) continue;
 					if (prune && eb > lim) continue;
-					const LocalRay L = to_local(ob, o, d);
+					LocalRay L;
+					to_local(L, ob, o, d);
 					if (ob.type == RT_OBJ_TRIMESH) {
 						// enter the mesh: remainder of this leaf, then the exit marker, then the mesh's nodes
 						if (i + 1 < count) { stk[sp] = leaf_ref(rank + 1, count - i - 1); stke[sp] = -RT_T_INF; sp++; }
@@ -167,62 +229,29 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode,
 						stke[sp] = -RT_T_INF;
 						sp++;
 						const DTree& T = S.mtrees[ob.mesh];
-						cur_obj = obj;
-						cur_rank = rank;
-						len = L.len;
-						item_off = (int)S.meshes[ob.mesh].item_off;
-						tris = S.tris + item_off;
+						V.obj = obj;
+						V.rank = rank;
+						V.len = L.len;
+						V.item_off = (int)S.meshes[ob.mesh].item_off;
+						V.have = false;
+						V.best_t = RT_T_INF;
+						V.best_pos = 0x7fffffff;
+						tris = S.tris + V.item_off;
 						nodes = S.mnodes2 + T.node_off;
 						o = L.o;
 						d = L.d;
-						I = make_inv(d, prune ? S.mesh_slack[ob.mesh] : 0.0);
+						make_inv(I, d, prune ? S.mesh_slack[ob.mesh] : 0.0);
 						level = 1;
-						lhave = false;
-						lbest_t = RT_T_INF;
-						lbest_pos = 0x7fffffff;
-						lim = lim_to_local(lim, len);
+						lim = lim_to_local(lim, V.len);
 						double er;
 						if (box_hit(T.lo, T.hi, o, d, I, er) && !(prune && er > lim)) cur = T.root;
 						break;
 					}
 					if (mode == TRAV_CLOSEST) {
-						LocalHit h;
-						int bf;
-						bool hit = false;
-						switch (ob.type) {
-						case RT_OBJ_SPHERE: hit = sphere_hit<false>(L.o, L.d, h); break;
-						case RT_OBJ_BOX: hit = box_prim_hit<false>(L.o, L.d, h, bf); break;
-						case RT_OBJ_SQUARE: hit = square_hit<false>(L.o, L.d, h); break;
-						case RT_OBJ_CYLINDER: hit = cylinder_hit<false>(L.o, L.d, h); break;
-						case RT_OBJ_CONE: hit = cone_hit<false>(L.o, L.d, ob.cone, ob.capped, h); break;
-						default: break;
-						}
-						if (hit) {
-							const double t = h.t / L.len;
-							if (!C.have || t < C.best_t || (t == C.best_t && rank < C.best_rank)) {
-								C.have = true;
-								C.best_t = t;
-								C.best_rank = rank;
-								C.best_obj = obj;
-								C.best_fpos = -1;
-								lim = t;
-							}
-						}
+						prim_closest(ob, L, rank, obj, C);
+						if (C.have) lim = C.best_t;
 					} else {
-						const ListEmit emit{S, ob, dw, L.len, (unsigned)rank, B};
-						switch (ob.type) {
-						case RT_OBJ_SPHERE: sphere_list(L.o, L.d, emit); break;
-						case RT_OBJ_BOX: box_list(L.o, L.d, emit); break;
-						case RT_OBJ_SQUARE: {
-							LocalHit h;
-							h.uv.x = h.uv.y = 0.0;
-							if (square_hit<true>(L.o, L.d, h)) emit(h.t, h.N, h.uv, 0);
-							break;
-						}
-						case RT_OBJ_CYLINDER: cylinder_list(L.o, L.d, emit); break;
-						case RT_OBJ_CONE: cone_list(L.o, L.d, ob.cone, ob.capped, emit); break;
-						default: break;
-						}
+						prim_list(S, ob, L, dw, rank, B);
 						lim = B.cut;
 					}
 				}
@@ -230,25 +259,26 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode,
 		}
 		// ---- 3. pop -----------------------------------------------------------------------------
 		if (cur == RT_REF_NONE) {
+#pragma unroll 1
 			for (;;) {
 				if (sp == 0) return;
 				sp--;
 				const int a = stk[sp];
 				if (a == RT_REF_MESH_EXIT) {
 					// Trimesh::intersectLocal's winner goes back to the scene level as one candidate
-					if (mode == TRAV_CLOSEST && lhave) {
-						const double t = lbest_t / len;
-						if (!C.have || t < C.best_t || (t == C.best_t && cur_rank < C.best_rank)) {
+					if (mode == TRAV_CLOSEST && V.have) {
+						const double t = V.best_t / V.len;
+						if (!C.have || t < C.best_t || (t == C.best_t && V.rank < C.best_rank)) {
 							C.have = true;
 							C.best_t = t;
-							C.best_rank = cur_rank;
-							C.best_obj = cur_obj;
-							C.best_fpos = item_off + lbest_pos;
+							C.best_rank = V.rank;
+							C.best_obj = V.obj;
+							C.best_fpos = V.item_off + V.best_pos;
 						}
 					}
 					o = ow;
 					d = dw;
-					I = make_inv(d, prune ? S.scene_slack : 0.0);
+					make_inv(I, d, prune ? S.scene_slack : 0.0);
 					nodes = S.snodes2;
 					level = 0;
 					lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : B.cut;
@@ -296,7 +326,7 @@ struct ShadowState {
 	int point;
 };
 
-RT_HD void shadow_begin(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& pos)
+RT_COLD void shadow_begin(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& pos)
 {
 	st.point = Lt.type != RT_LIGHT_DIRECTIONAL;
 	st.limit = RT_T_INF;
@@ -318,7 +348,7 @@ RT_HD void shadow_pass_reset(const ShadowState& st, SBuf& B)
 }
 // Consumes one collection pass.  Returns true when the attenuation is final (in st.sattn); false
 // when another pass (continuing after B.floor) is needed.
-RT_HD bool shadow_walk(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& dir, const rt_params& prm)
+RT_COLD bool shadow_walk(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& dir, const rt_params& prm)
 {
 	const bool overflow = B.min_dropped < RT_T_INF && B.min_dropped <= B.cut;
 	const bool aterm = prm.aterm_thresh > 0.0;

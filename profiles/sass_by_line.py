@@ -13,6 +13,8 @@ for ln in open(path):
     if ln.startswith(".text."):
         infn = key in ln
         continue
+    if infn and ln.startswith("$"):  # out-of-line device functions follow the kernel body
+        infn = False
     if not infn:
         continue
     m = re.match(r'\s*//## File "([^"]+)", line (\d+)', ln)

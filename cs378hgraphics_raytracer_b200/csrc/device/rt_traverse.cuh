@@ -140,9 +140,11 @@ struct MeshVisit {
 	int best_pos;
 };
 
-template <bool PRUNE>
-RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode, TravClosest& C, SBuf& B)
+// FIXED_MODE >= 0 compiles the walk for one query kind only (the wavefront's stage kernels)
+template <bool PRUNE, int FIXED_MODE = -1>
+RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B)
 {
+	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : mode_arg;
 	int stk[RT_STACK];
 	double stke[RT_STACK];
 	const bool prune = PRUNE || mode == TRAV_SHADOW;

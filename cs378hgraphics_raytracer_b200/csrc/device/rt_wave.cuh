@@ -1,0 +1,269 @@
+// rt_wave.cuh - the trace loop as a streaming wavefront: one small kernel per stage, rays in
+// HBM queues between them.
+//
+// Why: the per-ray code of this tracer is long, branchy FP64 (six primitive kinds, two tree
+// levels, textures, refraction, the sorted shadow walk).  Fused into one persistent kernel it is
+// instruction-fetch bound (profiles/r1_v2_*, r1_v3_*: 50-80 % of warp stalls are "no instruction",
+// the loop body does not fit the 32 KB L1.5 I-cache and every warp of an SM sits in a different
+// part of it), while HBM is idle (<1 % of peak).  So the stages are separate kernels - all warps of
+// an SM then run the same few KB of code - and the rays stream through HBM, which costs a few
+// hundred bytes per ray of a resource that is otherwise unused.
+//
+// One round (host loop in rt_api.cu: launch_wave):
+//   k_wave_gen      primary rays for up to W - |children| new camera samples   -> queue Cur
+//   k_wave_closest  Scene::intersect for every ray of the batch                -> hit records
+//   k_wave_shade    RayTracer::traceRay's body for every hit / miss: emission + ambient and the
+//                   background go to the sample accumulators; reflection / refraction rays are
+//                   appended to queue Nxt, one shadow ray per light to the shadow queue
+//   k_wave_shadow   Light::shadowAttenuation for every shadow ray; term * attenuation is added
+//                   to the sample
+// then Cur <-> Nxt.  The recursion's return value is carried forward as a weight (see RayTask in
+// rt_shade.cuh), so nothing ever waits for a child.  If a round's children exceed W, the excess is
+// spilled to a LIFO stack and taken back when a later round has room (depth-first, so memory stays
+// bounded by W * (depth + 2) rays).
+#pragma once
+
+namespace rtd {
+
+enum { KIND_DEAD = 7 }; // a primary slot outside the image (edge tiles): skipped by every stage
+
+#define RT_WAVE_THREADS 128
+
+// closest-hit rays: o[3] d[3] weight[3] att_kt[3] | sample | depth, att_mode, kind (pack_meta)
+// shadow rays     : o[3] d[3] term[3]             | sample | light
+struct RayQueue {
+	double* d;
+	int* i;
+	long long cap;
+	int nd; // doubles per entry: 12 or 9
+	__device__ __forceinline__ d3 load_v(int field, long long slot) const
+	{
+		return mk3(d[(field + 0) * cap + slot], d[(field + 1) * cap + slot], d[(field + 2) * cap + slot]);
+	}
+	__device__ __forceinline__ void store_v(int field, long long slot, const d3& v) const
+	{
+		d[(field + 0) * cap + slot] = v.x;
+		d[(field + 1) * cap + slot] = v.y;
+		d[(field + 2) * cap + slot] = v.z;
+	}
+	__device__ __forceinline__ void store_meta(long long slot, int a, int b) const
+	{
+		i[slot] = a;
+		i[cap + slot] = b;
+	}
+};
+
+// what k_wave_closest leaves for k_wave_shade: t < 0 = miss
+struct HitQueue {
+	double* t;
+	int2* of; // (object, global mesh item position or -1)
+};
+
+// device-side counters of one trace call
+struct WaveCounters {
+	unsigned long long stats[8]; // camera, reflection, refraction, shadow rays, overflow flag
+	unsigned long long n_children;
+	unsigned long long n_shadow;
+};
+
+// One entry per lane with pred set, appended to a queue shared by the whole grid: one atomic per
+// warp.  Every lane of the warp must call this.
+__device__ __forceinline__ long long wave_reserve(bool pred, unsigned lt_mask, unsigned long long* counter)
+{
+	const unsigned m = __ballot_sync(0xffffffffu, pred);
+	if (m == 0) return -1;
+	const int leader = __ffs(m) - 1;
+	unsigned long long base = 0;
+	if ((int)(threadIdx.x & 31) == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
+	base = __shfl_sync(0xffffffffu, base, leader);
+	return pred ? (long long)base + __popc(m & lt_mask) : -1;
+}
+
+// ---- stage 0: primary rays ------------------------------------------------------------------
+// slots [slot0, slot0 + n) of the launch's primary-ray space -> Q[dst ...]
+__global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue Q, long long dst, long long slot0, long long n)
+{
+	const long long k = (long long)blockIdx.x * RT_WAVE_THREADS + threadIdx.x;
+	if (k >= n) return;
+	const long long s = slot0 + k;
+	const long long smp = s / A.lenses;
+	const int lens = (int)(s % A.lenses);
+	d3 ro = mk3(0, 0, 0), rd = mk3(0, 0, 1);
+	bool ok = true;
+	if (A.src == SRC_RAYS) {
+		ro = ld3(A.rays[s].p);
+		rd = ld3(A.rays[s].d);
+	} else {
+		double x = 0, y = 0;
+		if (A.src == SRC_GRID) {
+			int pi_, pj_;
+			ok = grid_sample(A, smp, pi_, pj_, x, y);
+		} else {
+			x = A.xs[smp];
+			y = A.ys[smp];
+		}
+		if (ok) primary_ray(S.cam, A.prm, x, y, lens, A.eye_shift, ro, rd);
+	}
+	const long long q = dst + k;
+	Q.store_v(0, q, ro);
+	Q.store_v(3, q, rd);
+	Q.store_v(6, q, mk3(1.0, 1.0, 1.0));
+	Q.store_v(9, q, mk3(1.0, 1.0, 1.0));
+	Q.store_meta(q, (int)smp, pack_meta(A.depth, 0, ok ? KIND_CAMERA : KIND_DEAD, 0));
+}
+
+// ---- stage 1: Scene::intersect ----------------------------------------------------------------
+#ifndef RT_CLOSEST_MINB
+#define RT_CLOSEST_MINB 4
+#endif
+__global__ void __launch_bounds__(RT_WAVE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H)
+{
+	const long long k = (long long)blockIdx.x * RT_WAVE_THREADS + threadIdx.x;
+	if (k >= m) return;
+	const long long q = base + k;
+	const int meta = Q.i[Q.cap + q];
+	if (((meta >> 12) & 15) == KIND_DEAD) return;
+	const d3 ro = Q.load_v(0, q), rd = Q.load_v(3, q);
+	TravClosest C;
+	C.have = false;
+	C.best_t = RT_T_INF;
+	C.best_rank = 0x7fffffff;
+	C.best_obj = -1;
+	C.best_fpos = -1;
+	SBuf unused;
+	unused.n = 0;
+	unused.cut = RT_T_INF;
+	traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused);
+	H.t[k] = C.have ? C.best_t : -1.0;
+	H.of[k] = make_int2(C.best_obj, C.best_fpos);
+}
+
+// ---- stage 2: RayTracer::traceRay's body --------------------------------------------------------
+__global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_shade(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue Q, long long base, long long m, const HitQueue H,
+                                                                 const RayQueue Nxt, const RayQueue SQ, WaveCounters* cnt)
+{
+	const unsigned lane = threadIdx.x & 31;
+	const unsigned lt_mask = (1u << lane) - 1u;
+	const long long k = (long long)blockIdx.x * RT_WAVE_THREADS + threadIdx.x;
+	const long long q = base + k;
+	bool live = k < m;
+	int meta = 0, sample = 0;
+	if (live) {
+		meta = Q.i[Q.cap + q];
+		sample = Q.i[q];
+		if (((meta >> 12) & 15) == KIND_DEAD) live = false;
+	}
+	unsigned n_cam = 0, n_refl = 0, n_refr = 0, n_shadow = 0, overflow = 0;
+	bool lit = false, has_refl = false, has_refr = false;
+	RayTask kid[2];
+	MatEval me;
+	Hit h;
+	d3 w = mk3(0, 0, 0), hitP = mk3(0, 0, 0), rd = mk3(0, 0, 1);
+	if (live) {
+		const int kind = (meta >> 12) & 15;
+		const d3 ro = Q.load_v(0, q);
+		rd = Q.load_v(3, q);
+		const d3 weight = Q.load_v(6, q);
+		if (kind == KIND_CAMERA) n_cam = 1;
+		else if (kind == KIND_REFL) n_refl = 1;
+		else n_refr = 1;
+		const double t = H.t[k];
+		if (t < 0.0) {
+			accumulate(A.accum, sample, weight * miss_colour(S, A.prm, rd));
+		} else {
+			const int2 of = H.of[k];
+			h.obj = of.x;
+			h.fpos = of.y;
+			h.t = t;
+			finalize_hit(S, ro, rd, h);
+			w = apply_att(weight, Q.load_v(9, q), (meta >> 8) & 15, h.t);
+			eval_material(S, h, me);
+			accumulate(A.accum, sample, w * (me.ke + me.ka * ld3(S.glob.ambient)));
+			hitP = ro + h.t * rd;
+			lit = true;
+			spawn_children(me, h, ro, rd, w, (meta & 255) - 1, kid, has_refl, has_refr);
+		}
+	}
+	// reflection / refraction rays -> next round's queue
+	for (int c = 0; c < 2; c++) {
+		const long long s = wave_reserve(c == 0 ? has_refl : has_refr, lt_mask, &cnt->n_children);
+		if (s >= 0) {
+			if (s >= Nxt.cap) { overflow = 1; continue; }
+			Nxt.store_v(0, s, kid[c].o);
+			Nxt.store_v(3, s, kid[c].d);
+			Nxt.store_v(6, s, kid[c].weight);
+			Nxt.store_v(9, s, kid[c].att_kt);
+			Nxt.store_meta(s, sample, pack_meta(kid[c].depth, kid[c].att_mode, kid[c].kind, 0));
+		}
+	}
+	// one shadow ray per light (Material::shade's loop, material.cpp:50-66), light by light so
+	// that neighbouring entries of the shadow queue aim at the same light
+	if (__any_sync(0xffffffffu, lit)) {
+		for (int li = 0; li < S.n_lights; li++) {
+			const long long s = wave_reserve(lit, lt_mask, &cnt->n_shadow);
+			if (s >= 0) {
+				n_shadow++;
+				if (s >= SQ.cap) { overflow = 1; continue; }
+				d3 term, pb, sdir;
+				light_term(S.lights[li], me, hitP, h.N, rd, term, pb, sdir);
+				SQ.store_v(0, s, pb);
+				SQ.store_v(3, s, sdir);
+				SQ.store_v(6, s, w * term);
+				SQ.store_meta(s, sample, li);
+			}
+		}
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		n_cam += __shfl_down_sync(0xffffffffu, n_cam, o);
+		n_refl += __shfl_down_sync(0xffffffffu, n_refl, o);
+		n_refr += __shfl_down_sync(0xffffffffu, n_refr, o);
+		n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
+		overflow |= __shfl_down_sync(0xffffffffu, overflow, o);
+	}
+	if (lane == 0) {
+		if (n_cam) atomicAdd(cnt->stats + 0, (unsigned long long)n_cam);
+		if (n_refl) atomicAdd(cnt->stats + 1, (unsigned long long)n_refl);
+		if (n_refr) atomicAdd(cnt->stats + 2, (unsigned long long)n_refr);
+		if (n_shadow) atomicAdd(cnt->stats + 3, (unsigned long long)n_shadow);
+		if (overflow) atomicAdd(cnt->stats + 4, 1ull);
+	}
+}
+
+// ---- stage 3: Light::shadowAttenuation ------------------------------------------------------------
+#ifndef RT_SHADOW_MINB
+#define RT_SHADOW_MINB 3
+#endif
+__global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, const WaveCounters* cnt)
+{
+	const long long k = (long long)blockIdx.x * RT_WAVE_THREADS + threadIdx.x;
+	long long n = (long long)cnt->n_shadow;
+	if (n > SQ.cap) n = SQ.cap;
+	if (k >= n) return;
+	const d3 ro = SQ.load_v(0, k), rd = SQ.load_v(3, k);
+	const rt_light& Lt = S.lights[SQ.i[SQ.cap + k]];
+	ShadowState st;
+	SBuf B;
+	TravClosest unused;
+	unused.have = false;
+	shadow_begin(st, B, Lt, ro);
+	for (;;) {
+		shadow_pass_reset(st, B);
+		traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B);
+		if (shadow_walk(st, B, Lt, rd, A.prm)) break;
+	}
+	accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
+}
+
+// spill / take back: n entries of a 12-double queue, src[src0 ...] -> dst[dst0 ...]
+__global__ void __launch_bounds__(256) k_wave_move(const RayQueue src, long long src0, const RayQueue dst, long long dst0, long long n)
+{
+	const long long k = (long long)blockIdx.x * 256 + threadIdx.x;
+	if (k >= n) return;
+#pragma unroll
+	for (int f = 0; f < 12; f++) dst.d[f * dst.cap + dst0 + k] = src.d[f * src.cap + src0 + k];
+	dst.i[dst0 + k] = src.i[src0 + k];
+	dst.i[dst.cap + dst0 + k] = src.i[src.cap + src0 + k];
+}
+
+} // namespace rtd

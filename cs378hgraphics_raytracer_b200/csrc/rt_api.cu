@@ -27,14 +27,22 @@ struct rt_ctx {
 	int sm_count = 0;
 	int pool_blocks = 0;
 	// work buffers (grown on demand, reused across calls)
-	void* buf[16] = {nullptr};
-	size_t buf_bytes[16] = {0};
+	void* buf[32] = {nullptr};
+	size_t buf_bytes[32] = {0};
 	unsigned long long launches = 0;
+	// wavefront path
+	long long wave_width = 1 << 21;        // rays per round (RT_B200_WAVE overrides)
+	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
+	unsigned long long* pinned = nullptr;  // round counters read back by the host
+	cudaEvent_t ev_round = nullptr;
+	unsigned long long rounds = 0;
 };
 
 namespace {
 
-enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS };
+enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
+       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_COUNT };
+static_assert(B_COUNT <= 32, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
 	do {                                                                                                  \
@@ -86,7 +94,104 @@ rt_status check_params(rt_ctx* ctx, const rt_params* p)
 	return RT_OK;
 }
 
-// One launch of the wavefront kernel over n_slots primary-ray slots.
+static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+rt_status make_queue(rt_ctx* ctx, int bd, int bi, long long cap, int nd, RayQueue& Q)
+{
+	rt_status st;
+	if ((st = ensure(ctx, bd, (size_t)cap * nd * sizeof(double))) != RT_OK) return st;
+	if ((st = ensure(ctx, bi, (size_t)cap * 2 * sizeof(int))) != RT_OK) return st;
+	Q.d = (double*)ctx->buf[bd];
+	Q.i = (int*)ctx->buf[bi];
+	Q.cap = cap;
+	Q.nd = nd;
+	return RT_OK;
+}
+
+rt_status launch_pool(rt_ctx* ctx, PoolArgs& A);
+
+// The trace loop over n_slots primary-ray slots as a streaming wavefront (device/rt_wave.cuh).
+rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
+{
+	if (ctx->use_pool || A.prm.aterm_thresh > 0.0) return launch_pool(ctx, A); // adaptive termination needs the shadowed colour before it recurses
+	if (A.n_slots <= 0) return RT_OK;
+	const int L = ctx->S.n_lights;
+	long long W = ctx->wave_width;
+	const long long fit = ((A.n_slots + 1023) / 1024) * 1024;
+	if (W > fit) W = fit;
+	rt_status st;
+	RayQueue cur, nxt, sq, sp;
+	sp.d = nullptr; sp.i = nullptr; sp.cap = 0; sp.nd = 12;
+	if ((st = make_queue(ctx, B_WQ0_D, B_WQ0_I, 2 * W, 12, cur)) != RT_OK) return st;
+	if ((st = make_queue(ctx, B_WQ1_D, B_WQ1_I, 2 * W, 12, nxt)) != RT_OK) return st;
+	if ((st = make_queue(ctx, B_SQ_D, B_SQ_I, W * (L > 0 ? L : 1), 9, sq)) != RT_OK) return st;
+	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_WH_OF, (size_t)W * sizeof(int2))) != RT_OK) return st;
+	HitQueue H;
+	H.t = (double*)ctx->buf[B_WH_T];
+	H.of = (int2*)ctx->buf[B_WH_OF];
+	WaveCounters* cnt = (WaveCounters*)ctx->buf[B_SMALL];
+	A.stats = cnt->stats;
+	long long cur_n = 0, sp_n = 0, cam = 0;
+	for (;;) {
+		long long base = 0, m = 0;
+		if (cur_n > W) {
+			// more children than one round takes: the oldest go to the spill stack
+			const long long spill = cur_n - W;
+			if (!sp.d) {
+				const long long cap = W * ((A.depth < 30 ? A.depth : 30) + 2);
+				if ((st = make_queue(ctx, B_WSP_D, B_WSP_I, cap, 12, sp)) != RT_OK) return st;
+			}
+			if (sp_n + spill > sp.cap) { ctx->error = "wavefront spill stack overflow"; return RT_ERR_OVERFLOW; }
+			k_wave_move<<<blocks_for(spill, 256), 256, 0, ctx->stream>>>(cur, 0, sp, sp_n, spill);
+			ctx->launches++;
+			sp_n += spill;
+			base = spill;
+			m = W;
+		} else {
+			long long need = W - cur_n;
+			const long long un = need < sp_n ? need : sp_n;
+			if (un > 0) {
+				k_wave_move<<<blocks_for(un, 256), 256, 0, ctx->stream>>>(sp, sp_n - un, cur, cur_n, un);
+				ctx->launches++;
+				sp_n -= un;
+				cur_n += un;
+				need -= un;
+			}
+			const long long gen = need < A.n_slots - cam ? need : A.n_slots - cam;
+			if (gen > 0) {
+				k_wave_gen<<<blocks_for(gen, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, cur_n, cam, gen);
+				ctx->launches++;
+				cur_n += gen;
+				cam += gen;
+			}
+			m = cur_n;
+		}
+		if (m == 0) break;
+		CK(cudaMemsetAsync(&cnt->n_children, 0, 2 * sizeof(unsigned long long), ctx->stream));
+		k_wave_closest<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H);
+		k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq, cnt);
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
+		ctx->launches += 2;
+		if (L > 0) {
+			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
+			k_wave_shadow<<<blocks_for(m * L, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, sq, cnt);
+			ctx->launches++;
+		}
+		CK(cudaGetLastError());
+		CK(cudaEventSynchronize(ctx->ev_round)); // the host plans the next round while the shadow rays run
+		cur_n = (long long)ctx->pinned[0];
+		if (cur_n > nxt.cap) cur_n = nxt.cap; // overflow was flagged by the kernel
+		const RayQueue tmp = cur;
+		cur = nxt;
+		nxt = tmp;
+		ctx->rounds++;
+	}
+	return RT_OK;
+}
+
+// One launch of the fused persistent kernel over n_slots primary-ray slots.
 rt_status launch_pool(rt_ctx* ctx, PoolArgs& A)
 {
 	const int warps_per_block = RT_POOL_THREADS / 32;
@@ -147,6 +252,10 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	cudaEventCreate(&ctx->ev0);
 	cudaEventCreate(&ctx->ev1);
+	cudaEventCreateWithFlags(&ctx->ev_round, cudaEventDisableTiming);
+	if (cudaMallocHost((void**)&ctx->pinned, 64) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
+	if (const char* e = getenv("RT_B200_WAVE")) { const long long v = atoll(e); if (v >= 1024) ctx->wave_width = (v + 1023) / 1024 * 1024; }
+	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;
 	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_pool<true>, RT_POOL_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
@@ -164,8 +273,10 @@ void rt_destroy(rt_ctx* ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	free_scene(ctx);
-	for (int i = 0; i < 16; i++)
+	for (int i = 0; i < 32; i++)
 		if (ctx->buf[i]) cudaFree(ctx->buf[i]);
+	if (ctx->pinned) cudaFreeHost(ctx->pinned);
+	if (ctx->ev_round) cudaEventDestroy(ctx->ev_round);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -226,8 +337,6 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	return RT_OK;
 }
 
-static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
-
 rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int part, int n_parts, void** dev_rgb, rt_stats* stats)
 {
 	if (!ctx) return RT_ERR_ARG;
@@ -266,7 +375,7 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 		if ((st = ensure(ctx, B_ACCUM, (size_t)n_samples * 24)) != RT_OK) return st;
 		A.accum = (double*)ctx->buf[B_ACCUM];
 		CK(cudaMemsetAsync(A.accum, 0, (size_t)n_samples * 24, ctx->stream));
-		if ((st = launch_pool(ctx, A)) != RT_OK) return st;
+		if ((st = launch_wave(ctx, A)) != RT_OK) return st;
 		double* accum2 = nullptr;
 		if (p->anaglyph) { // second eye, shifted by ANAGLYPH_DELTA (RayTracer.cpp:23,92-99)
 			if ((st = ensure(ctx, B_ACCUM2, (size_t)n_samples * 24)) != RT_OK) return st;
@@ -275,7 +384,7 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 			PoolArgs A2 = A;
 			A2.accum = accum2;
 			A2.eye_shift = 0.25;
-			if ((st = launch_pool(ctx, A2)) != RT_OK) return st;
+			if ((st = launch_wave(ctx, A2)) != RT_OK) return st;
 		}
 		if (n_pix > 0) {
 			k_resolve_grid<<<blocks_for(n_pix, 256), 256, 0, ctx->stream>>>(A, accum2, n_pix, fb);
@@ -313,7 +422,7 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 			L.n_slots = n_samples * A.lenses;
 			CK(cudaMemsetAsync(L.accum, 0, (size_t)n_samples * 24, ctx->stream));
 			CK(cudaMemsetAsync(next_count, 0, 8, ctx->stream));
-			if ((st = launch_pool(ctx, L)) != RT_OK) return st;
+			if ((st = launch_wave(ctx, L)) != RT_OK) return st;
 			k_adapt_resolve<<<blocks_for(n_regions, 256), 256, 0, ctx->stream>>>((const Region*)ctx->buf[cur], n_regions, N, L.accum, *p, pixacc,
 			                                                                  (Region*)ctx->buf[nxt], next_count, (unsigned long long)n_regions * 4);
 			ctx->launches++;
@@ -407,7 +516,7 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 	A.accum = (double*)ctx->buf[B_ACCUM];
 	A.n_slots = (long long)n * A.lenses;
 	CK(cudaMemsetAsync(A.accum, 0, (size_t)n * 24, ctx->stream));
-	if ((st = launch_pool(ctx, A)) != RT_OK) return st;
+	if ((st = launch_wave(ctx, A)) != RT_OK) return st;
 	double* accum2 = nullptr;
 	if (p->anaglyph) {
 		if ((st = ensure(ctx, B_ACCUM2, (size_t)n * 24)) != RT_OK) return st;
@@ -416,7 +525,7 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 		PoolArgs A2 = A;
 		A2.accum = accum2;
 		A2.eye_shift = 0.25;
-		if ((st = launch_pool(ctx, A2)) != RT_OK) return st;
+		if ((st = launch_wave(ctx, A2)) != RT_OK) return st;
 	}
 	k_sample_values<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(A.accum, accum2, n, *p, (double*)ctx->buf[B_PIXACC]);
 	ctx->launches++;
@@ -459,7 +568,7 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
 		A.accum = (double*)ctx->buf[B_ACCUM];
 		A.n_slots = n;
 		CK(cudaMemsetAsync(A.accum, 0, (size_t)n * 24, ctx->stream));
-		if ((st = launch_pool(ctx, A)) != RT_OK) return st;
+		if ((st = launch_wave(ctx, A)) != RT_OK) return st;
 		CK(cudaMemcpyAsync(rgb_out, A.accum, (size_t)n * 24, cudaMemcpyDeviceToHost, ctx->stream));
 	}
 	return read_stats(ctx, nullptr, 0.f);

@@ -39,7 +39,8 @@ class Params(ctypes.Structure):
 
 class Stats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint64) for n in "camera_rays reflection_rays refraction_rays shadow_rays".split()] + \
-               [("device_ms", ctypes.c_double), ("launches", ctypes.c_uint64)]
+               [("device_ms", ctypes.c_double), ("launches", ctypes.c_uint64), ("cooperative_rays", ctypes.c_uint64),
+                ("rounds", ctypes.c_uint64)]
 
     @property
     def rays(self):

@@ -17,10 +17,45 @@
 // re-converging sections (while-while form): descend internal nodes / process one leaf / pop.
 #pragma once
 #include "rt_shadow.cuh"
+#if defined(RT_COUNT_WORK) && !defined(__CUDACC__)
+#include <cstdio>
+#include <cstdlib>
+#endif
 
 namespace rtd {
 
 enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1 };
+
+// Work counters for the cost model (scenes/cost_model.py): host build of tests/hostsim only.
+#if defined(RT_COUNT_WORK) && !defined(__CUDACC__)
+struct TravWork {
+	unsigned long long walks[2], nodes[2], tris[2], objs[2]; // per query kind, summed
+	unsigned long long hist[2][32];                           // walks by floor(log2(nodes + 1))
+	unsigned long long max_nodes[2];
+};
+inline thread_local TravWork g_work;
+inline unsigned long long g_work_dump = ~0ull; // print rays whose walk visits more nodes than this
+struct WorkScope {
+	int mode;
+	unsigned long long n0, t0;
+	const d3 &o, &d;
+	WorkScope(int m, const d3& o_, const d3& d_) : mode(m), n0(g_work.nodes[m]), t0(g_work.tris[m]), o(o_), d(d_) { g_work.walks[m]++; }
+	~WorkScope()
+	{
+		const unsigned long long n = g_work.nodes[mode] - n0;
+		if (n > g_work_dump) fprintf(stderr, "walk mode %d nodes %llu tris %llu o %.17g %.17g %.17g d %.17g %.17g %.17g\n", mode, n, g_work.tris[mode] - t0, o.x, o.y, o.z, d.x, d.y, d.z);
+		int b = 0;
+		while ((n + 1) >> (b + 1)) b++;
+		g_work.hist[mode][b]++;
+		if (n > g_work.max_nodes[mode]) g_work.max_nodes[mode] = n;
+	}
+};
+#define RT_CNT(f, m) (g_work.f[m]++)
+#define RT_WORK_SCOPE(m) WorkScope work_scope_(m, ow, dw)
+#else
+#define RT_CNT(f, m) ((void)0)
+#define RT_WORK_SCOPE(m) ((void)0)
+#endif
 
 struct TravClosest {
 	bool have;
@@ -140,11 +175,16 @@ struct MeshVisit {
 	int best_pos;
 };
 
-// FIXED_MODE >= 0 compiles the walk for one query kind only (the wavefront's stage kernels)
+// FIXED_MODE >= 0 compiles the walk for one query kind only (the wavefront's stage kernels).
+// budget > 0: give up after that many tree nodes and return false - the caller hands the ray to the
+// warp-cooperative walk (rt_coop.cuh).  A few rays visit thousands of nodes (a zero direction
+// component makes the reference's slab test accept every box along that axis, bbox.cc:43) and a
+// warp waits for its slowest lane; the result of an abandoned walk is not used.
 template <bool PRUNE, int FIXED_MODE = -1>
-RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B)
+RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B, int budget = 0)
 {
 	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : mode_arg;
+	RT_WORK_SCOPE(mode);
 	int stk[RT_STACK];
 	double stke[RT_STACK];
 	const bool prune = PRUNE || mode == TRAV_SHADOW;
@@ -165,7 +205,7 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 	V.best_t = RT_T_INF;
 	V.best_pos = 0x7fffffff;
 	double e;
-	if (!box_hit(S.stree.lo, S.stree.hi, o, d, I, e)) return;
+	if (!box_hit(S.stree.lo, S.stree.hi, o, d, I, e)) return true;
 	int sp = 0;
 	int cur = S.stree.root;
 	for (;;) {
@@ -173,6 +213,8 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 #pragma unroll 1
 		while (cur >= 0) {
 			const DNode2& n = nodes[cur];
+			RT_CNT(nodes, mode);
+			if (budget > 0 && --budget == 0) return false;
 			double e0, e1;
 			bool h0 = box_hit(n.lo0, n.hi0, o, d, I, e0);
 			bool h1 = box_hit(n.lo1, n.hi1, o, d, I, e1);
@@ -198,6 +240,7 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 					const int pos = first + i;
 					double t;
 					d3 bary;
+					RT_CNT(tris, mode);
 					if (!tri_hit<false>(tris[pos], o, d, t, bary)) continue;
 					if (mode == TRAV_CLOSEST) {
 						if (!V.have || t < V.best_t || (t == V.best_t && pos < V.best_pos)) {
@@ -217,6 +260,7 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 					const int rank = first + i;
 					const int obj = S.sitems[rank];
 					const rt_object& ob = S.objs[obj];
+					RT_CNT(objs, mode);
 					// Geometry::intersect / intersectList: world-bbox pretest (scene.cpp:15,43) is a real
 					// filter (leaf boxes are unions), then the object-space test
 					double eb;
@@ -263,7 +307,7 @@ RT_HD void traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 		if (cur == RT_REF_NONE) {
 #pragma unroll 1
 			for (;;) {
-				if (sp == 0) return;
+				if (sp == 0) return true;
 				sp--;
 				const int a = stk[sp];
 				if (a == RT_REF_MESH_EXIT) {

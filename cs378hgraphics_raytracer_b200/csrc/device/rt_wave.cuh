@@ -22,6 +22,7 @@
 // spilled to a LIFO stack and taken back when a later round has room (depth-first, so memory stays
 // bounded by W * (depth + 2) rays).
 #pragma once
+#include "rt_coop.cuh"
 
 namespace rtd {
 
@@ -61,9 +62,11 @@ struct HitQueue {
 
 // device-side counters of one trace call
 struct WaveCounters {
-	unsigned long long stats[8]; // camera, reflection, refraction, shadow rays, overflow flag
+	unsigned long long stats[8]; // camera, reflection, refraction, shadow rays, overflow flag, heavy rays
 	unsigned long long n_children;
 	unsigned long long n_shadow;
+	unsigned long long n_heavy;      // rays of this round that exhausted the node budget
+	unsigned long long heavy_cursor; // next heavy ray to be taken by a warp
 };
 
 // One entry per lane with pred set, appended to a queue shared by the whole grid: one atomic per
@@ -116,7 +119,8 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 #ifndef RT_CLOSEST_MINB
 #define RT_CLOSEST_MINB 4
 #endif
-__global__ void __launch_bounds__(RT_WAVE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H)
+__global__ void __launch_bounds__(RT_WAVE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
+                                                                                    int budget, int* heavy, WaveCounters* cnt)
 {
 	const long long k = (long long)blockIdx.x * RT_WAVE_THREADS + threadIdx.x;
 	if (k >= m) return;
@@ -133,9 +137,43 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_CLOSEST_MINB) k_wave_close
 	SBuf unused;
 	unused.n = 0;
 	unused.cut = RT_T_INF;
-	traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused);
+	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, budget)) {
+		heavy[atomicAdd(&cnt->n_heavy, 1ull)] = (int)k; // k_wave_closest_heavy redoes this ray
+		return;
+	}
 	H.t[k] = C.have ? C.best_t : -1.0;
 	H.of[k] = make_int2(C.best_obj, C.best_fpos);
+}
+
+// The rays that ran out of budget, one per warp (rt_coop.cuh); persistent grid, dynamic fetch.
+__global__ void __launch_bounds__(32 * RT_COOP_WARPS) k_wave_closest_heavy(const __grid_constant__ DScene S, const RayQueue Q, long long base, const HitQueue H, const int* heavy, WaveCounters* cnt)
+{
+	__shared__ CoopStack stacks[RT_COOP_WARPS];
+	CoopStack& K = stacks[threadIdx.x >> 5];
+	const unsigned lane = threadIdx.x & 31;
+	const unsigned long long n = cnt->n_heavy;
+	for (;;) {
+		unsigned long long j = 0;
+		if (lane == 0) j = atomicAdd(&cnt->heavy_cursor, 1ull);
+		j = __shfl_sync(0xffffffffu, j, 0);
+		if (j >= n) break;
+		const int k = heavy[j];
+		const long long q = base + k;
+		const d3 ro = Q.load_v(0, q), rd = Q.load_v(3, q);
+		TravClosest C;
+		C.have = false;
+		C.best_t = RT_T_INF;
+		C.best_rank = 0x7fffffff;
+		C.best_obj = -1;
+		C.best_fpos = -1;
+		coop_closest(S, ro, rd, C, K);
+		if (lane == 0) {
+			H.t[k] = C.have ? C.best_t : -1.0;
+			H.of[k] = make_int2(C.best_obj, C.best_fpos);
+		}
+		__syncwarp();
+	}
+	if (lane == 0 && threadIdx.x == 0 && blockIdx.x == 0 && n) atomicAdd(cnt->stats + 5, n);
 }
 
 // ---- stage 2: RayTracer::traceRay's body --------------------------------------------------------

@@ -32,6 +32,7 @@ struct rt_ctx {
 	unsigned long long launches = 0;
 	// wavefront path
 	long long wave_width = 1 << 21;        // rays per round (RT_B200_WAVE overrides)
+	int walk_budget = 512;                 // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
 	unsigned long long* pinned = nullptr;  // round counters read back by the host
 	cudaEvent_t ev_round = nullptr;
@@ -41,7 +42,7 @@ struct rt_ctx {
 namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
-       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_COUNT };
+       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_COUNT };
 static_assert(B_COUNT <= 32, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -127,6 +128,8 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if ((st = make_queue(ctx, B_SQ_D, B_SQ_I, W * (L > 0 ? L : 1), 9, sq)) != RT_OK) return st;
 	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_WH_OF, (size_t)W * sizeof(int2))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_HEAVY, (size_t)W * sizeof(int))) != RT_OK) return st;
+	int* heavy = (int*)ctx->buf[B_HEAVY];
 	HitQueue H;
 	H.t = (double*)ctx->buf[B_WH_T];
 	H.of = (int2*)ctx->buf[B_WH_OF];
@@ -168,8 +171,12 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 			m = cur_n;
 		}
 		if (m == 0) break;
-		CK(cudaMemsetAsync(&cnt->n_children, 0, 2 * sizeof(unsigned long long), ctx->stream));
-		k_wave_closest<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H);
+		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
+		k_wave_closest<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt);
+		if (ctx->walk_budget > 0) {
+			k_wave_closest_heavy<<<ctx->sm_count * 4, 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt);
+			ctx->launches++;
+		}
 		k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq, cnt);
 		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
@@ -228,6 +235,8 @@ rt_status read_stats(rt_ctx* ctx, rt_stats* stats, float ms)
 		stats->shadow_rays = h[3];
 		stats->device_ms = ms;
 		stats->launches = ctx->launches;
+		stats->cooperative_rays = h[5];
+		stats->rounds = ctx->rounds;
 	}
 	if (h[4]) { ctx->error = "device ray pool overflow"; return RT_ERR_OVERFLOW; }
 	return RT_OK;
@@ -256,6 +265,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (cudaMallocHost((void**)&ctx->pinned, 64) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	if (const char* e = getenv("RT_B200_WAVE")) { const long long v = atoll(e); if (v >= 1024) ctx->wave_width = (v + 1023) / 1024 * 1024; }
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) ctx->walk_budget = v; }
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;
 	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_pool<true>, RT_POOL_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
@@ -346,6 +356,7 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 	if (w <= 0 || h <= 0 || n_parts <= 0 || part < 0 || part >= n_parts || !dev_rgb) { ctx->error = "bad frame arguments"; return RT_ERR_ARG; }
 	CK(cudaSetDevice(ctx->device));
 	ctx->launches = 0;
+	ctx->rounds = 0;
 	PoolArgs A;
 	std::memset(&A, 0, sizeof(A));
 	A.prm = *p;
@@ -488,6 +499,7 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 	if (n == 0) return RT_OK;
 	CK(cudaSetDevice(ctx->device));
 	ctx->launches = 0;
+	ctx->rounds = 0;
 	// RayTracer::tracePixel's window coordinates (RayTracer.cpp:87-88)
 	const int s = (p->aa_mode != RT_AA_NONE && p->aa_mode != RT_AA_ADAPTIVE) ? p->aa_samples : 1;
 	std::vector<double> xs(n), ys(n);
@@ -544,6 +556,7 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
 	if (n == 0) return RT_OK;
 	CK(cudaSetDevice(ctx->device));
 	ctx->launches = 0;
+	ctx->rounds = 0;
 	if ((st = ensure(ctx, B_RAYS, (size_t)n * sizeof(rt_ray))) != RT_OK) return st;
 	CK(cudaMemcpyAsync(ctx->buf[B_RAYS], rays, (size_t)n * sizeof(rt_ray), cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaMemsetAsync(ctx->buf[B_SMALL], 0, 64, ctx->stream));

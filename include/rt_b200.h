@@ -82,6 +82,9 @@ typedef struct rt_stats {
 	uint64_t shadow_rays;
 	double device_ms;  /* CUDA-event time of the device work of this call */
 	uint64_t launches; /* kernels launched by this call */
+	uint64_t cooperative_rays; /* of the above, rays whose tree walk was finished by a whole warp
+	                              (they exhausted the single-thread node budget) */
+	uint64_t rounds;   /* wavefront rounds of this call */
 } rt_stats;
 
 typedef struct rt_ctx rt_ctx;

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <vector>
 #include <omp.h>
+#define RT_COUNT_WORK 1
 #include "rt_shade.cuh"
 #include "rt_derive.hpp"
 
@@ -168,6 +169,38 @@ int sim_render(const void* arena, const rt_params* prm, int w, int h, uint8_t* r
 			stats->shadow_rays += x.shadow_rays;
 		}
 	}
+	return 0;
+}
+
+
+// Work profile of one frame (cost model for bench.py's roofline, tail analysis): out[2][4 + 32 + 1] =
+// per query kind {walks, nodes, tris, objs, hist[32], max_nodes}
+int sim_work(const void* arena, const rt_params* prm, int w, int h, unsigned long long* out)
+{
+	Sim sim;
+	setup(sim, arena);
+	const int nt = omp_get_max_threads();
+	std::vector<TravWork> all(nt);
+	if (const char* e = getenv("RT_WORK_DUMP")) g_work_dump = strtoull(e, nullptr, 10);
+#pragma omp parallel
+	{
+		std::memset(&g_work, 0, sizeof(g_work));
+#pragma omp for collapse(2) schedule(dynamic, 16)
+		for (int j = 0; j < h; j++)
+			for (int i = 0; i < w; i++) {
+				const double x = double(i) / double(w), y = double(j) / double(h);
+				sample_colour<true>(sim.S, *prm, x, y, nullptr);
+			}
+		all[omp_get_thread_num()] = g_work;
+	}
+	std::memset(out, 0, 2 * 37 * sizeof(unsigned long long));
+	for (const TravWork& t : all)
+		for (int m = 0; m < 2; m++) {
+			unsigned long long* o = out + m * 37;
+			o[0] += t.walks[m]; o[1] += t.nodes[m]; o[2] += t.tris[m]; o[3] += t.objs[m];
+			for (int b = 0; b < 32; b++) o[4 + b] += t.hist[m][b];
+			if (t.max_nodes[m] > o[36]) o[36] = t.max_nodes[m];
+		}
 	return 0;
 }
 

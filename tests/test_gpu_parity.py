@@ -210,3 +210,30 @@ def test_division_selftest(ctx):
     assert ctx.selftest_division(1 << 28, seed=11, exp_range=40) == 0
     assert ctx.selftest_division(1 << 26, seed=12, exp_range=250) == 0
     assert ctx.selftest_division(1 << 24, seed=13, exp_range=0) == 0
+
+
+@pytest.mark.parametrize("scene", ["dragon_small.ray", "mixed_small.ray", "trimesh2.ray"])
+def test_cooperative_walk_same_frame(rtlib, oracle_mod, scene_dir, scene, monkeypatch):
+    """Rays that exhaust the single-thread node budget are finished by a whole warp
+    (device/rt_coop.cuh).  With the budget forced down to 3 nodes most mesh rays take that path;
+    frame and ray counts must not change."""
+    monkeypatch.setenv("RT_B200_BUDGET", "3")
+    c = rtlib.Context(0)
+    try:
+        path = scene_dir / scene
+        arena = rtlib.load_ray_file(str(path))
+        c.upload(arena)
+        orc = oracle_mod.Oracle(str(path))
+        w = 200
+        h = oracle_mod.frame_height(w, orc.aspect)
+        p = rtlib.Params.default(depth=5)
+        ref_img, ref_st, _ = orc.render(p, w, h)
+        img, st = c.render(p, w, h)
+        assert st.cooperative_rays > 1000
+        d = oracle_mod.image_diff(ref_img, img)
+        assert d["within1"] >= TOL_WITHIN1, d
+        assert d["exact"] >= 0.999, d
+        assert (st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays) == \
+            (ref_st.camera_rays, ref_st.reflection_rays, ref_st.refraction_rays, ref_st.shadow_rays)
+    finally:
+        c.close()

@@ -90,7 +90,7 @@ RT_HD d3 mul33(const double* m, d3 v)
 // against the hardware sequence bit for bit.
 struct RayInv {
 	d3 y;          // 1/d per axis (IEEE)
-	d3 sl;         // pruning slack per axis = slack/|d|
+	double slmax;  // pruning slack: max over the axes with d != 0 of slack/|d|
 	unsigned span; // width of the exponent window of `a` served by the FMA path: 1201, or 0 when
 	               // some |d| lies outside [2^-300, 2^300] (every quotient is then a real division)
 };
@@ -98,7 +98,11 @@ RT_HD bool div_range_ok(double d) { const double a = fabs(d); return d == 0.0 ||
 RT_COLD void make_inv(RayInv& I, const d3& d, double slack)
 {
 	I.y = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
-	I.sl = mk3(slack * fabs(I.y.x), slack * fabs(I.y.y), slack * fabs(I.y.z));
+	const d3 sl = mk3(slack * fabs(I.y.x), slack * fabs(I.y.y), slack * fabs(I.y.z));
+	I.slmax = 0.0;
+	if (d.x != 0.0) I.slmax = sl.x;
+	if (d.y != 0.0 && sl.y > I.slmax) I.slmax = sl.y;
+	if (d.z != 0.0 && sl.z > I.slmax) I.slmax = sl.z;
 	I.span = (div_range_ok(d.x) && div_range_ok(d.y) && div_range_ok(d.z)) ? 1201u : 0u;
 }
 RT_HD unsigned biased_exp(double a)

@@ -7,31 +7,65 @@ namespace rtd {
 
 // BoundingBox::intersect (reference ray/src/scene/bbox.cc:33-70).  The per-axis early returns
 // are monotone (tMin only grows, tMax only shrinks) so testing once after the loop is identical.
-// The six quotients come from div_by (rt_math.cuh): bit-identical to IEEE division.
-// `entry` receives tMin lowered by sl = slack/|d| per axis (precomputed per ray): a conservative entry distance used ONLY to
-// cull subtrees that cannot beat the current closest hit; box membership itself is decided by the
-// reference's exact arithmetic (see DESIGN.md "pruning without changing the winner").
-RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
+// `entry` receives tMin lowered by the ray's pruning slack: a conservative entry distance used
+// ONLY to cull subtrees that cannot beat the current closest hit; box membership itself is the
+// reference's decision (see DESIGN.md "pruning without changing the winner").
+//
+// box_hit_exact: the six quotients are correctly rounded (div_by, rt_math.cuh), i.e. the
+// reference's own numbers.
+RT_COLD bool box_hit_exact(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
 {
-	double tMin = -1.0e308, tMax = 1.0e308, en = -1.0e308;
-#define RT_SLAB(O, D, Y, LO, HI, SL)                                        \
+	double tMin = -1.0e308, tMax = 1.0e308;
+#define RT_SLAB(O, D, Y, LO, HI)                                            \
 	if (D != 0.0) {                                                         \
 		double t1 = div_by(LO - O, D, Y, I.span);                           \
 		double t2 = div_by(HI - O, D, Y, I.span);                           \
 		if (t1 > t2) { double tt = t1; t1 = t2; t2 = tt; }                  \
 		if (t1 > tMin) tMin = t1;                                           \
 		if (t2 < tMax) tMax = t2;                                           \
-		double e = t1 - SL;                                                 \
-		if (e > en) en = e;                                                 \
 	}
-	RT_SLAB(o.x, d.x, I.y.x, bmin[0], bmax[0], I.sl.x)
-	RT_SLAB(o.y, d.y, I.y.y, bmin[1], bmax[1], I.sl.y)
-	RT_SLAB(o.z, d.z, I.y.z, bmin[2], bmax[2], I.sl.z)
+	RT_SLAB(o.x, d.x, I.y.x, bmin[0], bmax[0])
+	RT_SLAB(o.y, d.y, I.y.y, bmin[1], bmax[1])
+	RT_SLAB(o.z, d.z, I.y.z, bmin[2], bmax[2])
 #undef RT_SLAB
-	entry = en;
+	entry = tMin - I.slmax;
 	if (tMin > tMax) return false;
 	if (tMax < RT_RAY_EPSILON) return false;
 	return true;
+}
+
+// box_hit: the same decision from ONE multiplication per quotient.  q~ = a * RN(1/d) differs from
+// the correctly rounded a/d by less than 3.4e-16 |q| (two roundings), and so do tMin~ = max of the
+// near quotients and tMax~ = min of the far ones from the exact tMin, tMax (max/min of perturbed
+// values move by at most the perturbation of the element that ends up selected, and an element
+// x <= T satisfies x + e|x| <= T + e|T|).  Hence with s = 1e-14 (|tMin~| + |tMax~|) (30x the bound):
+//     tMax~ - tMin~ < -s                   =>  exact tMin > tMax       : miss
+//     tMax~ < EPS - 1e-20                  =>  exact tMax < EPS        : miss
+//     tMax~ - tMin~ > s, tMax~ > EPS+1e-20 =>  neither                 : hit
+// and only the sliver in between (grazing rays, boxes touching the origin) takes box_hit_exact.
+// Non-finite or denormal intermediates fail all three tests and fall through to it as well.
+RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
+{
+	if (I.span != 0u) {
+		double tn = -1.0e308, tf = 1.0e308;
+#define RT_SLAB(O, D, Y, LO, HI)                                            \
+		if (D != 0.0) {                                                     \
+			const double q1 = (LO - O) * Y, q2 = (HI - O) * Y;              \
+			const double nr = q2 < q1 ? q2 : q1, fr = q2 < q1 ? q1 : q2;    \
+			if (nr > tn) tn = nr;                                           \
+			if (fr < tf) tf = fr;                                           \
+		}
+		RT_SLAB(o.x, d.x, I.y.x, bmin[0], bmax[0])
+		RT_SLAB(o.y, d.y, I.y.y, bmin[1], bmax[1])
+		RT_SLAB(o.z, d.z, I.y.z, bmin[2], bmax[2])
+#undef RT_SLAB
+		const double s = 1e-14 * (fabs(tn) + fabs(tf)) + 1e-290;
+		const double gap = tf - tn;
+		entry = tn - I.slmax;
+		if (gap < -s || tf < RT_RAY_EPSILON - 1e-20) return false;
+		if (gap > s && tf > RT_RAY_EPSILON + 1e-20) return true;
+	}
+	return box_hit_exact(bmin, bmax, o, d, I, entry);
 }
 
 // What a primitive's intersectLocal leaves in the isect (object space).

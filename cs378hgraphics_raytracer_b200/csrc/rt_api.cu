@@ -32,7 +32,7 @@ struct rt_ctx {
 	unsigned long long launches = 0;
 	// wavefront path
 	long long wave_width = 1 << 21;        // rays per round (RT_B200_WAVE overrides)
-	int walk_budget = 512;                 // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
+	int walk_budget = 96;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
 	unsigned long long* pinned = nullptr;  // round counters read back by the host
 	cudaEvent_t ev_round = nullptr;

@@ -29,6 +29,9 @@ namespace rtd {
 enum { KIND_DEAD = 7 }; // a primary slot outside the image (edge tiles): skipped by every stage
 
 #define RT_WAVE_THREADS 128
+#ifndef RT_TRACE_THREADS
+#define RT_TRACE_THREADS 64 // block size of the two tree-walk kernels: small blocks retire (and are replaced) sooner
+#endif
 
 // closest-hit rays: o[3] d[3] weight[3] att_kt[3] | sample | depth, att_mode, kind (pack_meta)
 // shadow rays     : o[3] d[3] term[3]             | sample | light
@@ -117,12 +120,12 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 
 // ---- stage 1: Scene::intersect ----------------------------------------------------------------
 #ifndef RT_CLOSEST_MINB
-#define RT_CLOSEST_MINB 4
+#define RT_CLOSEST_MINB 12 // 80 registers: the walk is latency bound, more resident warps beat fewer spills (profiles/r1_variants.txt)
 #endif
-__global__ void __launch_bounds__(RT_WAVE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
+__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
                                                                                     int budget, int* heavy, WaveCounters* cnt)
 {
-	const long long k = (long long)blockIdx.x * RT_WAVE_THREADS + threadIdx.x;
+	const long long k = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
 	if (k >= m) return;
 	const long long q = base + k;
 	const int meta = Q.i[Q.cap + q];
@@ -270,11 +273,11 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_shade(const __grid_con
 
 // ---- stage 3: Light::shadowAttenuation ------------------------------------------------------------
 #ifndef RT_SHADOW_MINB
-#define RT_SHADOW_MINB 3
+#define RT_SHADOW_MINB 10 // 96 registers
 #endif
-__global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, const WaveCounters* cnt)
+__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, const WaveCounters* cnt)
 {
-	const long long k = (long long)blockIdx.x * RT_WAVE_THREADS + threadIdx.x;
+	const long long k = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
 	long long n = (long long)cnt->n_shadow;
 	if (n > SQ.cap) n = SQ.cap;
 	if (k >= n) return;

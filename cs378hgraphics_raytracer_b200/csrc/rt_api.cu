@@ -172,7 +172,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		}
 		if (m == 0) break;
 		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
-		k_wave_closest<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt);
+		k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt);
 		if (ctx->walk_budget > 0) {
 			k_wave_closest_heavy<<<ctx->sm_count * 4, 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt);
 			ctx->launches++;
@@ -183,7 +183,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		ctx->launches += 2;
 		if (L > 0) {
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
-			k_wave_shadow<<<blocks_for(m * L, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, sq, cnt);
+			k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, A, sq, cnt);
 			ctx->launches++;
 		}
 		CK(cudaGetLastError());

@@ -204,14 +204,21 @@ def run_b200(args, key, wl, rank, world, local_rank):
         arena_bytes = a.bytes()
         a.free()
     arena_bytes = par.broadcast_arena(arena_bytes, rank, world, device)
-    par.upload_bytes(ctx, arena_bytes)
+    # the arena lives in page-locked host memory (the e2e step copies it to the device every time)
+    pinned = torch.empty(len(arena_bytes), dtype=torch.uint8, pin_memory=True)
+    pinned.numpy()[...] = np.frombuffer(arena_bytes, dtype=np.uint8)
+
+    def upload():
+        ctx._check(rt.lib().rt_upload_scene(ctx._h, ctypes.c_void_p(pinned.data_ptr()), pinned.numel()))
+
+    upload()
     hdr = np.frombuffer(arena_bytes[:32 + 17 * 24], dtype=np.uint64)
     cam = np.frombuffer(arena_bytes[int(hdr[4 + 3 * 1 + 1]):int(hdr[4 + 3 * 1 + 1]) + 14 * 8], dtype=np.float64)
     cam_aspect = float(cam[12])
     w = wl["w"]
     h = ob.frame_height(w, cam_aspect)
     n_items = int(hdr[4 + 3 * 12 + 2])
-    h2d_bytes = len(arena_bytes) + 96 * n_items
+    h2d_bytes = len(arena_bytes)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
 
     def barrier():
@@ -230,7 +237,7 @@ def run_b200(args, key, wl, rank, world, local_rank):
         return st, full
 
     def step_e2e(host_out):
-        par.upload_bytes(ctx, arena_bytes)
+        upload()
         if world == 1:
             _, st = ctx.render(params, w, h, out=host_out)
         else:
@@ -277,6 +284,20 @@ def run_b200(args, key, wl, rank, world, local_rank):
     barrier()
     e1 = time.perf_counter()
 
+    # per-stage device times: the same frames once more with CUDA events around every launch
+    # (rt_set_profiling); kept out of the timed region above because the extra events cost a few
+    # microseconds per launch
+    ctx.set_profiling(True)
+    stage_ms = np.zeros(6)
+    stage_n = np.zeros(6)
+    kind_rays = np.zeros(2)
+    for _ in range(args.steps):
+        st, _ = step_resident()
+        stage_ms += np.array(list(st.stage_ms))
+        stage_n += np.array(list(st.stage_launches))
+        kind_rays += np.array([st.camera_rays + st.reflection_rays + st.refraction_rays, st.shadow_rays], dtype=np.float64)
+    ctx.set_profiling(False)
+
     stats = torch.tensor([float(rays), float(e_rays), float(launches), elapsed, e1 - e0, dev_ms], dtype=torch.float64, device=device)
     if world > 1:
         sums = stats.clone()
@@ -298,18 +319,28 @@ def run_b200(args, key, wl, rank, world, local_rank):
                           "l2": "256 MiB L2 flush between timed frames (its own time subtracted)"},
                "clocks": clocks, "gpu_launches": tot_launches,
                "e2e": {"value": tot_e_rays / e_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": w * h * 3,
-                       "what": "rt_upload_scene (whole scene host->device) + render + RGB8 frame device->host, every step"}}
-        # roofline of the dominant kernel (k_trace_pool): algorithmic bytes per ray x rays / kernel time
+                       "what": "rt_upload_scene (whole scene arena, pinned host -> device, layouts rebuilt on the device) + render + RGB8 frame device -> host, every step"}}
+        # roofline of the dominant kernel (rank 0's stage times): algorithmic bytes of the rays that
+        # kernel walked (scenes/cost_model.json, per ray kind) / its device time
         cm = load_cost_model(key)
         peak, peak_src = measured_peaks()
-        if cm:
-            alg_bytes = cm["bytes_per_ray"] * (tot_rays / args.steps / world)
-            k_ms = dev_ms_max / args.steps
+        names = rt.Stats.STAGES
+        out["stages"] = {names[k]: {"ms_per_step": stage_ms[k] / args.steps, "launches_per_step": stage_n[k] / args.steps} for k in range(6) if stage_n[k] > 0}
+        if cm and stage_ms.sum() > 0:
+            closest_ms, shadow_ms = stage_ms[1] + stage_ms[2], stage_ms[4]
+            kind, kernel, k_ms, k_n = ("shadow", "k_wave_shadow", shadow_ms, stage_n[4]) if shadow_ms >= closest_ms else \
+                                      ("closest", "k_wave_closest (+ k_wave_closest_heavy)", closest_ms, stage_n[1])
+            ck = cm["kinds"][kind]
+            n_rays = kind_rays[0 if kind == "closest" else 1]
+            alg_bytes = ck["bytes_per_ray"] * n_rays
             ach = alg_bytes / (k_ms * 1e-3) / 1e9
-            out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": cm.get("dram_traffic_bytes"),
-                               "peak_source": peak_src, "kernel": "k_trace_pool", "kernel_ms": k_ms, "bytes_per_ray": cm["bytes_per_ray"],
-                               "fp64": {"flops_per_ray": cm.get("flops_per_ray"),
-                                        "achieved_tflops": (cm.get("flops_per_ray", 0) * tot_rays / args.steps / world) / (k_ms * 1e-3) / 1e12}}
+            out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                               "traffic": (cm.get("dram_traffic") or {}).get(kind), "peak_source": peak_src, "kernel": kernel,
+                               "kernel_ms_per_launch": k_ms / max(k_n, 1), "launches_per_step": k_n / args.steps,
+                               "algorithmic_bytes_per_launch": alg_bytes / max(k_n, 1), "bytes_per_ray": ck["bytes_per_ray"],
+                               "note": "the walk is FP64-latency bound, not bandwidth bound: the scene is L2 resident (DESIGN.md, roofline)",
+                               "fp64": {"flops_per_ray": ck["flops_per_ray"], "achieved_tflops": ck["flops_per_ray"] * n_rays / (k_ms * 1e-3) / 1e12,
+                                        "peak_tflops": 37.0}}
         else:
             out["roofline"] = None
         # the reference on this box's host cores, bounded sample (N = 1 only)

@@ -40,7 +40,9 @@ class Params(ctypes.Structure):
 class Stats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint64) for n in "camera_rays reflection_rays refraction_rays shadow_rays".split()] + \
                [("device_ms", ctypes.c_double), ("launches", ctypes.c_uint64), ("cooperative_rays", ctypes.c_uint64),
-                ("rounds", ctypes.c_uint64)]
+                ("rounds", ctypes.c_uint64), ("stage_ms", ctypes.c_double * 6), ("stage_launches", ctypes.c_uint64 * 6)]
+
+    STAGES = ("gen", "closest", "coop", "shade", "shadow", "other")
 
     @property
     def rays(self):
@@ -92,6 +94,10 @@ def lib():
     L.rt_trace_rays.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, ctypes.c_int, vp, vp]
     L.rt_selftest_division.argtypes = [vp, ctypes.c_longlong, ctypes.c_ulonglong, ctypes.c_int, ctypes.POINTER(ctypes.c_ulonglong)]
     L.rt_selftest_division.restype = i32
+    L.rt_selftest_derive.argtypes = [vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_ulonglong)]
+    L.rt_selftest_derive.restype = i32
+    L.rt_set_profiling.argtypes = [vp, ctypes.c_int]
+    L.rt_set_profiling.restype = i32
     L.rt_load_ray_file.argtypes = [cp, vp, ctypes.POINTER(vp), ctypes.POINTER(sz)]
     L.rt_arena_free.argtypes = [vp]
     L.rt_arena_free.restype = None
@@ -201,6 +207,15 @@ class Context:
         dev = ctypes.c_void_p()
         self._check(lib().rt_render_device(self._h, ctypes.byref(params), w, h, part, n_parts, ctypes.byref(dev), ctypes.byref(st)))
         return dev.value, st
+
+    def selftest_derive(self, arena):
+        bad = ctypes.c_ulonglong()
+        self._check(lib().rt_selftest_derive(self._h, arena.ptr, arena.nbytes, ctypes.byref(bad)))
+        return bad.value
+
+    def set_profiling(self, on):
+        """rt_set_profiling: per-stage CUDA-event times in Stats.stage_ms."""
+        self._check(lib().rt_set_profiling(self._h, 1 if on else 0))
 
     def selftest_division(self, n, seed=1, exp_range=40):
         bad = ctypes.c_ulonglong()

@@ -80,7 +80,13 @@ static bool tree_ok(const rt_node* n, uint64_t n_nodes, uint64_t n_items, uint64
 	return true;
 }
 
-rt_status rt_arena_validate(const void* arena, size_t bytes)
+static rt_status validate_impl(const void* arena, size_t bytes, bool deep);
+rt_status rt_arena_validate(const void* arena, size_t bytes) { return validate_impl(arena, bytes, true); }
+// header, section table, small tables; the per-element index checks are left to the caller
+// (rt_upload_scene runs them on the device)
+rt_status rt_arena_validate_tables(const void* arena, size_t bytes) { return validate_impl(arena, bytes, false); }
+
+static rt_status validate_impl(const void* arena, size_t bytes, bool deep)
 {
 	if (!arena || bytes < sizeof(rt_arena_header)) return RT_ERR_ARG;
 	rt::ArenaView A(arena);
@@ -113,8 +119,9 @@ rt_status rt_arena_validate(const void* arena, size_t bytes)
 		if (ob[k].type < 0 || ob[k].type > RT_OBJ_TRIMESH || ob[k].material < 0 || (uint64_t)ob[k].material >= n_mat) return RT_ERR_ARG;
 		if (ob[k].type == RT_OBJ_TRIMESH && (ob[k].mesh < 0 || (uint64_t)ob[k].mesh >= n_mesh)) return RT_ERR_ARG;
 	}
-	if (!tree_ok(A.ptr<rt_node>(RT_SEC_SCENE_NODES), A.count(RT_SEC_SCENE_NODES), A.count(RT_SEC_SCENE_ITEMS), n_obj, A.ptr<int32_t>(RT_SEC_SCENE_ITEMS)))
+	if (deep && !tree_ok(A.ptr<rt_node>(RT_SEC_SCENE_NODES), A.count(RT_SEC_SCENE_NODES), A.count(RT_SEC_SCENE_ITEMS), n_obj, A.ptr<int32_t>(RT_SEC_SCENE_ITEMS)))
 		return RT_ERR_ARG;
+	uint64_t prev_node_end = 0, prev_item_end = 0;
 	const rt_mesh* ms = A.ptr<rt_mesh>(RT_SEC_MESHES);
 	const rt_face* fc = A.ptr<rt_face>(RT_SEC_FACES);
 	for (uint64_t k = 0; k < n_mesh; k++) {
@@ -124,6 +131,11 @@ rt_status rt_arena_validate(const void* arena, size_t bytes)
 		if (m.vnorm_off >= 0 && (uint64_t)m.vnorm_off + m.vert_cnt > A.count(RT_SEC_VNORMALS)) return RT_ERR_ARG;
 		if (m.vmat_off >= 0 && (uint64_t)m.vmat_off + m.vert_cnt > A.count(RT_SEC_VMATS)) return RT_ERR_ARG;
 		if (m.object < 0 || (uint64_t)m.object >= n_obj || m.node_cnt == 0) return RT_ERR_ARG;
+		// meshes lie back to back in ascending order (the device kernels locate a node's mesh by bisection)
+		if (m.node_off < prev_node_end || m.item_off < prev_item_end) return RT_ERR_ARG;
+		prev_node_end = m.node_off + m.node_cnt;
+		prev_item_end = m.item_off + m.item_cnt;
+		if (!deep) continue;
 		for (uint64_t f = 0; f < m.face_cnt; f++)
 			for (int v = 0; v < 3; v++)
 				if (fc[m.face_off + f].ids[v] < 0 || (uint64_t)fc[m.face_off + f].ids[v] >= m.vert_cnt) return RT_ERR_ARG;
@@ -131,7 +143,7 @@ rt_status rt_arena_validate(const void* arena, size_t bytes)
 			return RT_ERR_ARG;
 	}
 	const int32_t* vm = A.ptr<int32_t>(RT_SEC_VMATS);
-	for (uint64_t k = 0; k < A.count(RT_SEC_VMATS); k++)
+	for (uint64_t k = 0; deep && k < A.count(RT_SEC_VMATS); k++)
 		if (vm[k] < 0 || (uint64_t)vm[k] >= n_mat) return RT_ERR_ARG;
 	return RT_OK;
 }

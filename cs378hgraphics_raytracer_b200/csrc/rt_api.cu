@@ -13,6 +13,9 @@
 #include "rt_arena_writer.hpp"
 #include "device/rt_kernels.cuh"
 #include "device/rt_derive.hpp"
+#include "device/rt_derive_dev.cuh"
+
+extern "C" rt_status rt_arena_validate_tables(const void* arena, size_t bytes); // host/host_api.cpp
 
 using namespace rtd;
 
@@ -27,23 +30,31 @@ struct rt_ctx {
 	int sm_count = 0;
 	int pool_blocks = 0;
 	// work buffers (grown on demand, reused across calls)
-	void* buf[32] = {nullptr};
-	size_t buf_bytes[32] = {0};
+	void* buf[48] = {nullptr};
+	size_t buf_bytes[48] = {0};
 	unsigned long long launches = 0;
 	// wavefront path
 	long long wave_width = 1 << 21;        // rays per round (RT_B200_WAVE overrides)
 	int walk_budget = 96;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
+	bool budget_auto = true;               // no RT_B200_BUDGET given: the budget adapts to the scene
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
 	unsigned long long* pinned = nullptr;  // round counters read back by the host
 	cudaEvent_t ev_round = nullptr;
 	unsigned long long rounds = 0;
+	// optional per-stage timing
+	bool profile = false;
+	std::vector<cudaEvent_t> ev_pool;
+	size_t ev_used = 0;
+	struct Span { int stage; cudaEvent_t a, b; };
+	std::vector<Span> spans;
 };
 
 namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
-       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_COUNT };
-static_assert(B_COUNT <= 32, "rt_ctx::buf too small");
+       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY,
+       B_ARENA, B_SNODES2, B_MNODES2, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_COUNT };
+static_assert(B_COUNT <= 48, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
 	do {                                                                                                  \
@@ -111,6 +122,25 @@ rt_status make_queue(rt_ctx* ctx, int bd, int bi, long long cap, int nd, RayQueu
 
 rt_status launch_pool(rt_ctx* ctx, PoolArgs& A);
 
+cudaEvent_t next_event(rt_ctx* ctx)
+{
+	if (ctx->ev_used == ctx->ev_pool.size()) {
+		cudaEvent_t e = nullptr;
+		cudaEventCreate(&e);
+		ctx->ev_pool.push_back(e);
+	}
+	return ctx->ev_pool[ctx->ev_used++];
+}
+// STAGE(id, launch): the launch, bracketed by events when profiling is on
+#define STAGE(id, ...)                                                        \
+	do {                                                                      \
+		cudaEvent_t a_ = nullptr, b_ = nullptr;                               \
+		if (ctx->profile) { a_ = next_event(ctx); b_ = next_event(ctx); cudaEventRecord(a_, ctx->stream); } \
+		__VA_ARGS__;                                                          \
+		ctx->launches++;                                                      \
+		if (ctx->profile) { cudaEventRecord(b_, ctx->stream); ctx->spans.push_back({id, a_, b_}); } \
+	} while (0)
+
 // The trace loop over n_slots primary-ray slots as a streaming wavefront (device/rt_wave.cuh).
 rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 {
@@ -146,8 +176,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 				if ((st = make_queue(ctx, B_WSP_D, B_WSP_I, cap, 12, sp)) != RT_OK) return st;
 			}
 			if (sp_n + spill > sp.cap) { ctx->error = "wavefront spill stack overflow"; return RT_ERR_OVERFLOW; }
-			k_wave_move<<<blocks_for(spill, 256), 256, 0, ctx->stream>>>(cur, 0, sp, sp_n, spill);
-			ctx->launches++;
+			STAGE(RT_STAGE_OTHER, k_wave_move<<<blocks_for(spill, 256), 256, 0, ctx->stream>>>(cur, 0, sp, sp_n, spill));
 			sp_n += spill;
 			base = spill;
 			m = W;
@@ -155,16 +184,14 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 			long long need = W - cur_n;
 			const long long un = need < sp_n ? need : sp_n;
 			if (un > 0) {
-				k_wave_move<<<blocks_for(un, 256), 256, 0, ctx->stream>>>(sp, sp_n - un, cur, cur_n, un);
-				ctx->launches++;
+				STAGE(RT_STAGE_OTHER, k_wave_move<<<blocks_for(un, 256), 256, 0, ctx->stream>>>(sp, sp_n - un, cur, cur_n, un));
 				sp_n -= un;
 				cur_n += un;
 				need -= un;
 			}
 			const long long gen = need < A.n_slots - cam ? need : A.n_slots - cam;
 			if (gen > 0) {
-				k_wave_gen<<<blocks_for(gen, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, cur_n, cam, gen);
-				ctx->launches++;
+				STAGE(RT_STAGE_GEN, k_wave_gen<<<blocks_for(gen, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, cur_n, cam, gen));
 				cur_n += gen;
 				cam += gen;
 			}
@@ -172,24 +199,24 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		}
 		if (m == 0) break;
 		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
-		k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt);
-		if (ctx->walk_budget > 0) {
-			k_wave_closest_heavy<<<ctx->sm_count * 4, 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt);
-			ctx->launches++;
-		}
-		k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq, cnt);
-		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt));
+		if (ctx->walk_budget > 0)
+			STAGE(RT_STAGE_COOP, k_wave_closest_heavy<<<ctx->sm_count * 4, 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt));
+		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq, cnt));
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
-		ctx->launches += 2;
 		if (L > 0) {
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
-			k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, A, sq, cnt);
-			ctx->launches++;
+			STAGE(RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, A, sq, cnt));
 		}
 		CK(cudaGetLastError());
 		CK(cudaEventSynchronize(ctx->ev_round)); // the host plans the next round while the shadow rays run
 		cur_n = (long long)ctx->pinned[0];
 		if (cur_n > nxt.cap) cur_n = nxt.cap; // overflow was flagged by the kernel
+		// the node budget follows the scene: if more than ~1.5 % of a round's rays ran out of it, the
+		// ordinary walk of this scene is simply longer (deep scene-level trees) - double it.  Either
+		// path gives the same hit, so this only moves work between the two kernels.
+		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)ctx->pinned[2] * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
 		const RayQueue tmp = cur;
 		cur = nxt;
 		nxt = tmp;
@@ -237,6 +264,11 @@ rt_status read_stats(rt_ctx* ctx, rt_stats* stats, float ms)
 		stats->launches = ctx->launches;
 		stats->cooperative_rays = h[5];
 		stats->rounds = ctx->rounds;
+		for (int k = 0; k < 6; k++) { stats->stage_ms[k] = 0.0; stats->stage_launches[k] = 0; }
+		for (const rt_ctx::Span& sp : ctx->spans) {
+			float t = 0.f;
+			if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess) { stats->stage_ms[sp.stage] += t; stats->stage_launches[sp.stage]++; }
+		}
 	}
 	if (h[4]) { ctx->error = "device ray pool overflow"; return RT_ERR_OVERFLOW; }
 	return RT_OK;
@@ -265,7 +297,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (cudaMallocHost((void**)&ctx->pinned, 64) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	if (const char* e = getenv("RT_B200_WAVE")) { const long long v = atoll(e); if (v >= 1024) ctx->wave_width = (v + 1023) / 1024 * 1024; }
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
-	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) ctx->walk_budget = v; }
+	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;
 	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_pool<true>, RT_POOL_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
@@ -283,8 +315,9 @@ void rt_destroy(rt_ctx* ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	free_scene(ctx);
-	for (int i = 0; i < 32; i++)
+	for (int i = 0; i < 48; i++)
 		if (ctx->buf[i]) cudaFree(ctx->buf[i]);
+	for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
 	if (ctx->pinned) cudaFreeHost(ctx->pinned);
 	if (ctx->ev_round) cudaEventDestroy(ctx->ev_round);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -295,10 +328,58 @@ void rt_destroy(rt_ctx* ctx)
 
 const char* rt_last_error(const rt_ctx* ctx) { return ctx ? ctx->error.c_str() : "null context"; }
 
+rt_status rt_set_profiling(rt_ctx* ctx, int on)
+{
+	if (!ctx) return RT_ERR_ARG;
+	ctx->profile = on != 0;
+	return RT_OK;
+}
+
+// Builds the traversal layouts of one group of trees on the device (device/rt_derive_dev.cuh).
+// nodes: cnt reference nodes in pre-order (n_mesh trees back to back, or the scene tree when
+// n_mesh == 0).  *max_depth receives the deepest node's depth (bit 31: deeper than 128).
+static rt_status derive_trees(rt_ctx* ctx, const rt_node* nodes, long long cnt, const rt_mesh* ms, int n_mesh, long long scene_items,
+                              int b_nodes2, int b_pre, unsigned* err, unsigned* max_depth)
+{
+	rt_status st;
+	if ((st = ensure(ctx, b_nodes2, (size_t)(cnt > 0 ? cnt : 1) * sizeof(DNode2))) != RT_OK) return st;
+	if ((st = ensure(ctx, b_pre, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_TMP_A, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_TMP_B, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_TMP_C, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_TMP_D, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
+	if (cnt <= 0) return RT_OK;
+	int* flag = (int*)ctx->buf[B_TMP_A];
+	int* pre = (int*)ctx->buf[b_pre];
+	const unsigned g = blocks_for(cnt, 256);
+	k_derive_flags<<<g, 256, 0, ctx->stream>>>(nodes, cnt, flag);
+	size_t tmp_bytes = 0;
+	CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flag, pre, (int)cnt, ctx->stream));
+	if ((st = ensure(ctx, B_CUBTMP, tmp_bytes)) != RT_OK) return st;
+	CK(cub::DeviceScan::ExclusiveSum(ctx->buf[B_CUBTMP], tmp_bytes, flag, pre, (int)cnt, ctx->stream));
+	k_derive_nodes2<<<g, 256, 0, ctx->stream>>>(nodes, cnt, pre, ms, n_mesh, scene_items, (DNode2*)ctx->buf[b_nodes2], err);
+	// depth: parent links + 7 rounds of pointer jumping (covers depth <= 128)
+	int* anc[2] = {(int*)ctx->buf[B_TMP_A], (int*)ctx->buf[B_TMP_C]};
+	int* dist[2] = {(int*)ctx->buf[B_TMP_B], (int*)ctx->buf[B_TMP_D]};
+	k_depth_self<<<g, 256, 0, ctx->stream>>>(cnt, anc[0], dist[0]);
+	k_depth_init<<<g, 256, 0, ctx->stream>>>(nodes, cnt, ms, n_mesh, anc[0], dist[0]);
+	int cur = 0;
+	for (int r = 0; r < 7; r++) {
+		k_depth_jump<<<g, 256, 0, ctx->stream>>>(cnt, anc[cur], dist[cur], anc[cur ^ 1], dist[cur ^ 1]);
+		cur ^= 1;
+	}
+	k_depth_max<<<g, 256, 0, ctx->stream>>>(cnt, anc[cur], dist[cur], max_depth);
+	ctx->launches += 12;
+	CK(cudaGetLastError());
+	return RT_OK;
+}
+
 rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 {
 	if (!ctx) return RT_ERR_ARG;
-	if (rt_arena_validate(arena, bytes) != RT_OK) { ctx->error = "invalid arena"; return RT_ERR_ARG; }
+	// header, section table and the small tables are checked here; the O(scene) index checks run
+	// on the device next to the layout kernels (rt_arena_validate does all of them on the host)
+	if (rt_arena_validate_tables(arena, bytes) != RT_OK) { ctx->error = "invalid arena"; return RT_ERR_ARG; }
 	CK(cudaSetDevice(ctx->device));
 	rt::ArenaView A(arena);
 	const rt_light* lights = A.ptr<rt_light>(RT_SEC_LIGHTS);
@@ -307,43 +388,108 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 			ctx->error = "area and spot lights are not implemented on the device path yet";
 			return RT_ERR_UNSUPPORTED;
 		}
-	Derived D;
-	derive(A, D);
-	if (D.max_scene_depth + D.max_mesh_depth > RT_STACK - 4 || A.count(RT_SEC_MESH_ITEMS) >= (1ull << 29) || A.count(RT_SEC_SCENE_ITEMS) >= (1ull << 29)) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
-	free_scene(ctx);
+	const long long n_snodes = (long long)A.count(RT_SEC_SCENE_NODES), n_mnodes = (long long)A.count(RT_SEC_MESH_NODES);
+	const long long n_mitems = (long long)A.count(RT_SEC_MESH_ITEMS), n_sitems = (long long)A.count(RT_SEC_SCENE_ITEMS);
+	const int n_mesh = (int)A.count(RT_SEC_MESHES);
+	if (n_mitems >= (1ll << 29) || n_sitems >= (1ll << 29) || n_mnodes >= 0x7fffffffll || n_snodes >= 0x7fffffffll || n_snodes == 0) {
+		ctx->error = "scene too large for 32-bit node references";
+		return RT_ERR_UNSUPPORTED;
+	}
+	ctx->has_scene = false;
+	rt_status st;
+	// one copy of the whole arena
+	if ((st = ensure(ctx, B_ARENA, bytes)) != RT_OK) return st;
+	uint8_t* dev = (uint8_t*)ctx->buf[B_ARENA];
+	CK(cudaMemcpyAsync(dev, arena, bytes, cudaMemcpyHostToDevice, ctx->stream));
 	DScene& S = ctx->S;
 	std::memset(&S, 0, sizeof(S));
-	rt_status st;
-#define UP(field, type, sec)                                                                        \
-	if ((st = upload<type>(ctx, A.ptr<type>(sec), A.count(sec), &S.field)) != RT_OK) { free_scene(ctx); return st; }
-	if ((st = upload<DNode2>(ctx, D.snodes2.data(), D.snodes2.size(), &S.snodes2)) != RT_OK) { free_scene(ctx); return st; }
-	if ((st = upload<DNode2>(ctx, D.mnodes2.data(), D.mnodes2.size(), &S.mnodes2)) != RT_OK) { free_scene(ctx); return st; }
-	if ((st = upload<DTree>(ctx, D.mtrees.data(), D.mtrees.size(), &S.mtrees)) != RT_OK) { free_scene(ctx); return st; }
-	UP(snodes, rt_node, RT_SEC_SCENE_NODES)
-	UP(sitems, int32_t, RT_SEC_SCENE_ITEMS)
-	UP(objs, rt_object, RT_SEC_OBJECTS)
-	UP(meshes, rt_mesh, RT_SEC_MESHES)
-	UP(mnodes, rt_node, RT_SEC_MESH_NODES)
-	UP(mitems, int32_t, RT_SEC_MESH_ITEMS)
-	UP(faces, rt_face, RT_SEC_FACES)
-	UP(mats, rt_material, RT_SEC_MATERIALS)
-	UP(lights, rt_light, RT_SEC_LIGHTS)
-	UP(texs, rt_texture, RT_SEC_TEXTURES)
-	UP(texdata, uint8_t, RT_SEC_TEXDATA)
-	UP(vmats, int32_t, RT_SEC_VMATS)
-#undef UP
-	if ((st = upload<double>(ctx, A.ptr<double>(RT_SEC_VERTS), A.count(RT_SEC_VERTS) * 3, &S.verts)) != RT_OK) { free_scene(ctx); return st; }
-	if ((st = upload<double>(ctx, A.ptr<double>(RT_SEC_VNORMALS), A.count(RT_SEC_VNORMALS) * 3, &S.vnormals)) != RT_OK) { free_scene(ctx); return st; }
-	if ((st = upload<DTri>(ctx, D.tris.data(), D.tris.size(), &S.tris)) != RT_OK) { free_scene(ctx); return st; }
-	if ((st = upload<double>(ctx, D.mesh_slack.data(), D.mesh_slack.size(), &S.mesh_slack)) != RT_OK) { free_scene(ctx); return st; }
+#define SEC(field, type, sec) S.field = (const type*)(dev + A.hdr->sections[sec].offset)
+	SEC(snodes, rt_node, RT_SEC_SCENE_NODES);
+	SEC(sitems, int32_t, RT_SEC_SCENE_ITEMS);
+	SEC(objs, rt_object, RT_SEC_OBJECTS);
+	SEC(meshes, rt_mesh, RT_SEC_MESHES);
+	SEC(mnodes, rt_node, RT_SEC_MESH_NODES);
+	SEC(mitems, int32_t, RT_SEC_MESH_ITEMS);
+	SEC(faces, rt_face, RT_SEC_FACES);
+	SEC(mats, rt_material, RT_SEC_MATERIALS);
+	SEC(lights, rt_light, RT_SEC_LIGHTS);
+	SEC(texs, rt_texture, RT_SEC_TEXTURES);
+	SEC(texdata, uint8_t, RT_SEC_TEXDATA);
+	SEC(vmats, int32_t, RT_SEC_VMATS);
+	SEC(verts, double, RT_SEC_VERTS);
+	SEC(vnormals, double, RT_SEC_VNORMALS);
+#undef SEC
+	unsigned* flags = (unsigned*)((unsigned long long*)ctx->buf[B_SMALL] + 28); // err, scene depth, mesh depth
+	CK(cudaMemsetAsync(flags, 0, 3 * sizeof(unsigned), ctx->stream));
+	if ((st = derive_trees(ctx, S.snodes, n_snodes, nullptr, 0, n_sitems, B_SNODES2, B_PRE_S, flags, flags + 1)) != RT_OK) return st;
+	if ((st = derive_trees(ctx, S.mnodes, n_mnodes, S.meshes, n_mesh, 0, B_MNODES2, B_PRE_M, flags, flags + 2)) != RT_OK) return st;
+	if ((st = ensure(ctx, B_MTREES, (size_t)(n_mesh > 0 ? n_mesh : 1) * sizeof(DTree))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_MSLACK, (size_t)(n_mesh > 0 ? n_mesh : 1) * sizeof(double))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_TRIS, (size_t)(n_mitems > 0 ? n_mitems : 1) * sizeof(DTri))) != RT_OK) return st;
+	if (n_mesh > 0) {
+		k_derive_mesh<<<blocks_for(n_mesh, 256), 256, 0, ctx->stream>>>(S.meshes, n_mesh, S.mnodes, (const int*)ctx->buf[B_PRE_M], (DTree*)ctx->buf[B_MTREES], (double*)ctx->buf[B_MSLACK]);
+		if (n_mitems > 0)
+			k_derive_tris<<<blocks_for(n_mitems, 256), 256, 0, ctx->stream>>>(S.meshes, n_mesh, S.mitems, S.faces, S.verts, n_mitems, (DTri*)ctx->buf[B_TRIS], flags);
+	}
+	{
+		const long long n_vm = (long long)A.count(RT_SEC_VMATS);
+		const long long n = n_sitems > n_vm ? n_sitems : n_vm;
+		if (n > 0) k_derive_check<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(S.sitems, n_sitems, (long long)A.count(RT_SEC_OBJECTS), S.vmats, n_vm, (long long)A.count(RT_SEC_MATERIALS), flags);
+	}
+	CK(cudaGetLastError());
+	S.snodes2 = (const DNode2*)ctx->buf[B_SNODES2];
+	S.mnodes2 = (const DNode2*)ctx->buf[B_MNODES2];
+	S.mtrees = (const DTree*)ctx->buf[B_MTREES];
+	S.mesh_slack = (const double*)ctx->buf[B_MSLACK];
+	S.tris = (const DTri*)ctx->buf[B_TRIS];
 	S.cam = *A.ptr<rt_camera>(RT_SEC_CAMERA);
 	S.glob = *A.ptr<rt_globals>(RT_SEC_GLOBALS);
-	S.scene_slack = D.scene_slack;
-	S.stree = D.stree;
+	// the scene tree's descriptor from its root node (host side: one node)
+	const rt_node& root = A.ptr<rt_node>(RT_SEC_SCENE_NODES)[0];
+	S.scene_slack = 1e-9 * box_extent(root);
+	for (int a = 0; a < 3; a++) { S.stree.lo[a] = root.bmin[a]; S.stree.hi[a] = root.bmax[a]; }
+	S.stree.root = root.right >= 0 ? 0 : leaf_ref(root.first, root.count);
+	S.stree.pad = 0;
+	S.stree.node_off = 0;
 	S.n_lights = (int)A.count(RT_SEC_LIGHTS);
 	S.n_objs = (int)A.count(RT_SEC_OBJECTS);
-	CK(cudaStreamSynchronize(ctx->stream)); // D's host vectors die with this scope
+	unsigned hflags[3];
+	CK(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream)); // also: the caller may reuse `arena` on return
+	if (hflags[0]) { ctx->error = "invalid arena: index out of range (device check " + std::to_string(hflags[0]) + ")"; return RT_ERR_ARG; }
+	if ((hflags[1] | hflags[2]) & 0x80000000u || hflags[1] + hflags[2] > RT_STACK - 4) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
+	if (ctx->budget_auto) ctx->walk_budget = 96;
 	ctx->has_scene = true;
+	return RT_OK;
+}
+
+// Device self-test: the layouts built by the device kernels of the last rt_upload_scene are
+// compared byte for byte with the host construction (device/rt_derive.hpp) from the same arena.
+rt_status rt_selftest_derive(rt_ctx* ctx, const void* arena, size_t bytes, unsigned long long* mismatches)
+{
+	if (!ctx || !mismatches) return RT_ERR_ARG;
+	if (!ctx->has_scene) { ctx->error = "no scene uploaded"; return RT_ERR_NO_SCENE; }
+	if (rt_arena_validate(arena, bytes) != RT_OK) { ctx->error = "invalid arena"; return RT_ERR_ARG; }
+	CK(cudaSetDevice(ctx->device));
+	rt::ArenaView A(arena);
+	Derived D;
+	derive(A, D);
+	unsigned long long bad = 0;
+	auto cmp = [&](const void* devp, const void* hostp, size_t n) -> rt_status {
+		std::vector<uint8_t> tmp(n);
+		if (n) CK(cudaMemcpy(tmp.data(), devp, n, cudaMemcpyDeviceToHost));
+		for (size_t k = 0; k < n; k++) bad += tmp[k] != ((const uint8_t*)hostp)[k];
+		return RT_OK;
+	};
+	rt_status st;
+	if ((st = cmp(ctx->S.snodes2, D.snodes2.data(), D.snodes2.size() * sizeof(DNode2))) != RT_OK) return st;
+	if ((st = cmp(ctx->S.mnodes2, D.mnodes2.data(), D.mnodes2.size() * sizeof(DNode2))) != RT_OK) return st;
+	if ((st = cmp(ctx->S.mtrees, D.mtrees.data(), D.mtrees.size() * sizeof(DTree))) != RT_OK) return st;
+	if ((st = cmp(ctx->S.tris, D.tris.data(), D.tris.size() * sizeof(DTri))) != RT_OK) return st;
+	if ((st = cmp(ctx->S.mesh_slack, D.mesh_slack.data(), D.mesh_slack.size() * sizeof(double))) != RT_OK) return st;
+	bad += std::memcmp(&ctx->S.stree, &D.stree, sizeof(DTree)) != 0;
+	bad += ctx->S.scene_slack != D.scene_slack;
+	*mismatches = bad;
 	return RT_OK;
 }
 
@@ -357,6 +503,8 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 	CK(cudaSetDevice(ctx->device));
 	ctx->launches = 0;
 	ctx->rounds = 0;
+	ctx->spans.clear();
+	ctx->ev_used = 0;
 	PoolArgs A;
 	std::memset(&A, 0, sizeof(A));
 	A.prm = *p;
@@ -500,6 +648,8 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 	CK(cudaSetDevice(ctx->device));
 	ctx->launches = 0;
 	ctx->rounds = 0;
+	ctx->spans.clear();
+	ctx->ev_used = 0;
 	// RayTracer::tracePixel's window coordinates (RayTracer.cpp:87-88)
 	const int s = (p->aa_mode != RT_AA_NONE && p->aa_mode != RT_AA_ADAPTIVE) ? p->aa_samples : 1;
 	std::vector<double> xs(n), ys(n);
@@ -557,6 +707,8 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
 	CK(cudaSetDevice(ctx->device));
 	ctx->launches = 0;
 	ctx->rounds = 0;
+	ctx->spans.clear();
+	ctx->ev_used = 0;
 	if ((st = ensure(ctx, B_RAYS, (size_t)n * sizeof(rt_ray))) != RT_OK) return st;
 	CK(cudaMemcpyAsync(ctx->buf[B_RAYS], rays, (size_t)n * sizeof(rt_ray), cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaMemsetAsync(ctx->buf[B_SMALL], 0, 64, ctx->stream));

@@ -85,7 +85,12 @@ typedef struct rt_stats {
 	uint64_t cooperative_rays; /* of the above, rays whose tree walk was finished by a whole warp
 	                              (they exhausted the single-thread node budget) */
 	uint64_t rounds;   /* wavefront rounds of this call */
+	/* per-stage device time (CUDA events around every launch) and launch counts; filled only
+	 * after rt_set_profiling(ctx, 1).  Stages: RT_STAGE_* below. */
+	double stage_ms[6];
+	uint64_t stage_launches[6];
 } rt_stats;
+enum { RT_STAGE_GEN = 0, RT_STAGE_CLOSEST = 1, RT_STAGE_COOP = 2, RT_STAGE_SHADE = 3, RT_STAGE_SHADOW = 4, RT_STAGE_OTHER = 5 };
 
 typedef struct rt_ctx rt_ctx;
 
@@ -95,10 +100,14 @@ typedef struct rt_ctx rt_ctx;
 rt_status rt_create(int device, rt_ctx** out);
 void rt_destroy(rt_ctx* ctx);
 const char* rt_last_error(const rt_ctx* ctx);
+/* on != 0: bracket every kernel launch of the trace loop with CUDA events and report per-stage
+ * times in rt_stats (a few microseconds per launch; off by default). */
+rt_status rt_set_profiling(rt_ctx* ctx, int on);
 
 /* Replaces what RayTracer::loadScene leaves behind for the tracer (RayTracer.cpp:196-240): the
- * arena (include/rt_arena.h) is validated, copied to HBM and re-laid-out for traversal.  The
- * caller keeps ownership of `arena`. */
+ * arena (include/rt_arena.h) is copied to HBM in one transfer (fastest from page-locked memory),
+ * validated and re-laid-out for traversal by device kernels.  The caller keeps ownership of
+ * `arena` and may reuse it on return. */
 rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes);
 
 /* RayTracer::traceImage(w,h) + getBuffer (RayTracer.cpp:279-314,184-189): renders the whole
@@ -127,6 +136,10 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
  * reciprocal division (device/rt_math.cuh div_by) are compared bit for bit with IEEE division;
  * exponents of a and d are drawn from [-exp_range, exp_range].  *mismatches must come back 0. */
 rt_status rt_selftest_division(rt_ctx* ctx, long long n, unsigned long long seed, int exp_range, unsigned long long* mismatches);
+
+/* Device self-test: the traversal layouts that rt_upload_scene built on the device from `arena`
+ * (the arena of the last upload) are compared byte for byte with the host construction. */
+rt_status rt_selftest_derive(rt_ctx* ctx, const void* arena, size_t bytes, unsigned long long* mismatches);
 
 /* ---- host-side scene loading (no GPU needed) -------------------------------------------- */
 /* Replaces Tokenizer + Parser::parseScene + Scene::add/conclude + Trimesh::conclude (reference

@@ -44,6 +44,7 @@ def main():
     subprocess.check_call(["make", "-s", "-C", d])
     S = ctypes.CDLL(os.path.join(d, "libhostsim.so"))
     S.sim_work.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    S.sim_render.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
     out = {}
     keys = sys.argv[1:] or ["c1", "c2", "c3", "c4", "c5"]
     path_json = os.path.join(ROOT, "scenes", "cost_model.json")
@@ -61,6 +62,10 @@ def main():
         buf = np.zeros(2 * 37, np.uint64)
         assert S.sim_work(arena.ptr, ctypes.byref(p), w, h, buf.ctypes.data) == 0
         buf = buf.reshape(2, 37)
+        img = np.zeros((h, w, 3), np.uint8)
+        st = rt.Stats()
+        assert S.sim_render(arena.ptr, ctypes.byref(p), w, h, img.ctypes.data, ctypes.byref(st)) == 0
+        n_rays = {0: st.camera_rays + st.reflection_rays + st.refraction_rays, 1: st.shadow_rays}
         kinds = {}
         tot_rays = 0
         tot_bytes = 0.0
@@ -70,12 +75,16 @@ def main():
             hist = [int(x) for x in buf[m, 4:36]]
             while hist and hist[-1] == 0:
                 hist.pop()
-            kinds[name] = dict(walks=walks, nodes_per_walk=nodes / max(walks, 1), tris_per_walk=tris / max(walks, 1),
-                               objs_per_walk=objs / max(walks, 1), max_nodes=int(buf[m, 36]), hist_log2_nodes=hist)
-            tot_rays += walks
-            tot_bytes += nodes * NODE_B + tris * TRI_B + objs * OBJ_B + walks * RAY_RECORD_B[m]
-            tot_flops += nodes * NODE_F + tris * TRI_F + objs * OBJ_F
-        out[key] = dict(workload=wl["name"], sampled_at="%dx%d, pinhole rays, depth %d" % (w, h, p.depth), walks=tot_rays,
+            rays = int(n_rays[m])
+            kb = nodes * NODE_B + tris * TRI_B + objs * OBJ_B + rays * RAY_RECORD_B[m]
+            kf = nodes * NODE_F + tris * TRI_F + objs * OBJ_F
+            kinds[name] = dict(rays=rays, walks=walks, nodes_per_ray=nodes / max(rays, 1), tris_per_ray=tris / max(rays, 1),
+                               objs_per_ray=objs / max(rays, 1), bytes_per_ray=kb / max(rays, 1), flops_per_ray=kf / max(rays, 1),
+                               max_nodes=int(buf[m, 36]), hist_log2_nodes=hist)
+            tot_rays += rays
+            tot_bytes += kb
+            tot_flops += kf
+        out[key] = dict(workload=wl["name"], sampled_at="%dx%d, pinhole rays, depth %d" % (w, h, p.depth), rays=tot_rays,
                         bytes_per_ray=tot_bytes / tot_rays, flops_per_ray=tot_flops / tot_rays, kinds=kinds)
         print(key, json.dumps(out[key]))
         sys.stdout.flush()

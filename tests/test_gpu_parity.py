@@ -237,3 +237,31 @@ def test_cooperative_walk_same_frame(rtlib, oracle_mod, scene_dir, scene, monkey
             (ref_st.camera_rays, ref_st.reflection_rays, ref_st.refraction_rays, ref_st.shadow_rays)
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("scene", SCENES)
+def test_device_built_layouts_match_host(rtlib, ctx, scene_dir, scene):
+    """rt_upload_scene builds the wide nodes / triangle records / tree descriptors with device
+    kernels; the host construction (rt_derive.hpp, the one tests/hostsim walks) must agree byte
+    for byte."""
+    arena = rtlib.load_ray_file(str(scene_dir / scene))
+    ctx.upload(arena)
+    assert ctx.selftest_derive(arena) == 0
+
+
+def test_upload_rejects_bad_indices(rtlib, ctx, scene_dir):
+    """The O(scene) index checks run on the device during the upload."""
+    arena = rtlib.load_ray_file(str(scene_dir / "trimesh2.ray"))
+    buf = bytearray(arena.bytes())
+    hdr = np.frombuffer(bytes(buf[:32 + 17 * 24]), dtype=np.uint64)
+    sec_items = 12  # RT_SEC_MESH_ITEMS
+    off = int(hdr[4 + 3 * sec_items + 1])
+    buf[off:off + 4] = (0x7fffff00).to_bytes(4, "little")
+    bad = np.frombuffer(bytes(buf), dtype=np.uint8).copy()
+    L = rtlib.lib()
+    import ctypes
+    st = L.rt_upload_scene(ctx._h, ctypes.c_void_p(bad.ctypes.data), len(bad))
+    assert st == 1  # RT_ERR_ARG
+    # and the context still works afterwards
+    ctx.upload(arena)
+    assert ctx.selftest_derive(arena) == 0

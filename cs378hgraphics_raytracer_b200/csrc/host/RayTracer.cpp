@@ -1,0 +1,120 @@
+// RayTracer.cpp - see RayTracer.h.  Every method names the reference member it stands in for.
+#include "RayTracer.h"
+#include <cstdio>
+#include <cstring>
+#include "rt_arena_writer.hpp"
+
+namespace rtb200 {
+
+RayTracer::RayTracer(int device) : stopTrace(false), ctx(nullptr), arena(nullptr), arena_bytes(0), loaded(false), buffer_width(256), buffer_height(256)
+{
+	rt_params_default(&ui);
+	std::memset(&stats, 0, sizeof(stats));
+	// the reference starts with a 256x256 buffer (RayTracer.cpp:176-182)
+	buffer.assign((size_t)buffer_width * buffer_height * 3, 0);
+	const rt_status st = rt_create(device, &ctx);
+	if (st != RT_OK) alert(st == RT_ERR_NO_DEVICE ? "no CUDA device: the device path has no CPU fallback" : "rt_create failed");
+}
+
+RayTracer::~RayTracer()
+{
+	if (arena) rt_arena_free(arena);
+	if (ctx) rt_destroy(ctx);
+}
+
+void RayTracer::alert(const std::string& msg)
+{
+	alert_msg = msg;
+	std::fprintf(stderr, "%s\n", msg.c_str()); // CommandLineUI::alert (ui/CommandLineUI.cpp:192-195)
+}
+
+bool RayTracer::loadScene(const char* fn)
+{
+	loaded = false;
+	if (!ctx) { alert("no device context"); return false; }
+	if (arena) { rt_arena_free(arena); arena = nullptr; }
+	const char* faces[6];
+	for (int k = 0; k < 6 && cubemap.size() == 6; k++) faces[k] = cubemap[k].c_str();
+	rt_status st = rt_load_ray_file(fn, cubemap.size() == 6 ? faces : nullptr, &arena, &arena_bytes);
+	if (st != RT_OK) { alert(rt_host_last_error()); return false; } // the reference alerts the parser's message and returns false
+	st = rt_upload_scene(ctx, arena, arena_bytes);
+	if (st != RT_OK) { alert(rt_last_error(ctx)); return false; }
+	loaded = true;
+	return true;
+}
+
+double RayTracer::aspectRatio()
+{
+	if (!loaded) return 1.0; // RayTracer.cpp:193
+	rt::ArenaView A(arena);
+	return A.ptr<rt_camera>(RT_SEC_CAMERA)->aspect;
+}
+
+void RayTracer::traceSetup(int w, int h)
+{
+	if (buffer_width != w || buffer_height != h) {
+		buffer_width = w;
+		buffer_height = h;
+		buffer.assign((size_t)w * h * 3, 0);
+	} else {
+		std::fill(buffer.begin(), buffer.end(), (unsigned char)0);
+	}
+}
+
+void RayTracer::traceImage(int w, int h)
+{
+	traceSetup(w, h);
+	if (!loaded) return;
+	const rt_status st = rt_render(ctx, &ui, w, h, buffer.data(), &stats);
+	if (st != RT_OK) alert(rt_last_error(ctx));
+}
+
+dvec3 RayTracer::tracePixel(int i, int j)
+{
+	dvec3 col = {0, 0, 0};
+	if (!loaded) return col;
+	const int32_t ij[2] = {i, j};
+	double rgb[3] = {0, 0, 0};
+	if (rt_trace_pixels(ctx, &ui, buffer_width, buffer_height, ij, 1, rgb) != RT_OK) { alert(rt_last_error(ctx)); return col; }
+	col = {rgb[0], rgb[1], rgb[2]};
+	setPixel(i, j, col); // tracePixel writes the pixel it traced (RayTracer.cpp:100)
+	return col;
+}
+
+dvec3 RayTracer::traceRay(ray& r, double thresh, int depth, double& length, dvec3*)
+{
+	dvec3 col = {0, 0, 0};
+	if (!loaded) return col;
+	rt_params p = ui;
+	p.aterm_thresh = thresh;
+	rt_ray rr = {{r.p.x, r.p.y, r.p.z}, {r.d.x, r.d.y, r.d.z}};
+	rt_hit hit;
+	double rgb[3];
+	if (rt_trace_rays(ctx, &p, &rr, 1, depth, &hit, rgb) != RT_OK) { alert(rt_last_error(ctx)); return col; }
+	if (hit.obj >= 0) length = hit.t; // `t = i.getT()` only on a hit (RayTracer.cpp:122)
+	col = {rgb[0], rgb[1], rgb[2]};
+	return col;
+}
+
+dvec3 RayTracer::getPixel(int i, int j)
+{
+	const unsigned char* px = buffer.data() + ((size_t)i + (size_t)j * buffer_width) * 3;
+	return {px[0] / 255.0, px[1] / 255.0, px[2] / 255.0};
+}
+
+void RayTracer::setPixel(int i, int j, dvec3 color)
+{
+	unsigned char* px = buffer.data() + ((size_t)i + (size_t)j * buffer_width) * 3;
+	px[0] = (unsigned char)(int)(255.0 * color.x);
+	px[1] = (unsigned char)(int)(255.0 * color.y);
+	px[2] = (unsigned char)(int)(255.0 * color.z);
+}
+
+void RayTracer::getBuffer(unsigned char*& buf, int& w, int& h)
+{
+	buf = buffer.empty() ? nullptr : buffer.data();
+	w = buffer_width;
+	h = buffer_height;
+}
+
+} // namespace rtb200

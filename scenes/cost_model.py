@@ -1,22 +1,20 @@
 #!/usr/bin/env python3
-"""Cost model of the bench workloads: algorithmic bytes and FP64 operations per ray.
+"""Cost model of the bench workloads: SURVEY.md 8(d)'s algorithmic work per ray.
 
 The per-ray DEVICE code, compiled for the host with work counters (tests/hostsim, RT_COUNT_WORK),
-renders each workload's scene from its camera at a reduced resolution and counts, per tree walk
-(one ray = one walk; shadow rays may take more than one collection pass):
-    nodes  two-child tree nodes visited   (128 B each: both child boxes + child refs)
-    tris   triangle tests                 ( 96 B each: 3 vertices + face normal)
-    objs   scene-level candidates tested  (192 B: bbox + inverse transform of the object record)
-and the fixed per-ray record traffic of the wavefront (queue entry written + read, hit record,
-accumulator update).  These are ALGORITHMIC bytes: what the walk must touch if nothing were cached;
-the roofline in bench.py divides them by the measured kernel time.
+renders each workload's scene from its camera at a reduced resolution with the ORDERED, PRUNED walk
+(the 8(d) "ordered-traversal lower bound" - not the reference's exhaustive walk) and counts per ray
+kind (closest-hit rays = camera + reflection + refraction; shadow rays):
+    nodes  two-child tree nodes visited, both tree levels      N_box = walks + 2 * nodes
+    tris   triangle tests in entered leaves                      N_tri
+    objs   scene-level candidates tested (bbox + transform)      N_obj = N_xform
+and applies the fixed formulas of SURVEY.md 8(d):
+    bytes/ray = 64 N_box + 128 N_tri + 192 N_obj + 96
+    flops/ray = 12 N_box + 150 N_tri + 60 N_obj + 40 N_xform + 120 N_shade_light
+(N_shade_light = one per shadow ray, charged to the shadow kind).  These are ALGORITHMIC figures:
+what the walk must touch if nothing were cached; bench.py divides them by measured kernel time.
 
-FP64 operation counts per unit (counted from the source, FMA = 2):
-    node: 2 boxes x (6 sub + 6 x (1 mul + 4 fma) + 3 sub) = 2 x 63 = 126 flop, ~40 compares/selects
-    tri : plane 5+5+1 div, point 6, three edge tests 3 x (6 sub + 9 + 5) = 60, area 20  ~ 100 flop
-    obj : bbox 63 + world->object transform 2 x 24 + normalise 12                        ~ 125 flop
-
-Writes scenes/cost_model.json.  Run here (CPU container), results are committed.
+Writes scenes/cost_model.json.  Run here (CPU container); the result is committed.
 """
 import ctypes
 import json
@@ -31,9 +29,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 sys.path.insert(0, os.path.join(ROOT, "scenes"))
 
-NODE_B, TRI_B, OBJ_B = 128, 96, 192
-NODE_F, TRI_F, OBJ_F = 126, 100, 125
-RAY_RECORD_B = {0: 2 * 104 + 16 + 16 + 24, 1: 2 * 80 + 24}  # closest: queue w+r, hit w+r, accum; shadow: queue w+r, accum
+BOX_B, TRI_B, OBJ_B, RAY_B = 64, 128, 192, 96
+BOX_F, TRI_F, OBJ_F, XFORM_F, SHADE_F = 12, 150, 60, 40, 120
 
 
 def main():
@@ -76,8 +73,9 @@ def main():
             while hist and hist[-1] == 0:
                 hist.pop()
             rays = int(n_rays[m])
-            kb = nodes * NODE_B + tris * TRI_B + objs * OBJ_B + rays * RAY_RECORD_B[m]
-            kf = nodes * NODE_F + tris * TRI_F + objs * OBJ_F
+            n_box = walks + 2 * nodes
+            kb = n_box * BOX_B + tris * TRI_B + objs * OBJ_B + rays * RAY_B
+            kf = n_box * BOX_F + tris * TRI_F + objs * (OBJ_F + XFORM_F) + (rays * SHADE_F if m == 1 else 0)
             kinds[name] = dict(rays=rays, walks=walks, nodes_per_ray=nodes / max(rays, 1), tris_per_ray=tris / max(rays, 1),
                                objs_per_ray=objs / max(rays, 1), bytes_per_ray=kb / max(rays, 1), flops_per_ray=kf / max(rays, 1),
                                max_nodes=int(buf[m, 36]), hist_log2_nodes=hist)

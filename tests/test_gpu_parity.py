@@ -265,3 +265,28 @@ def test_upload_rejects_bad_indices(rtlib, ctx, scene_dir):
     # and the context still works afterwards
     ctx.upload(arena)
     assert ctx.selftest_derive(arena) == 0
+
+
+def test_cli_renders_reference_frame(rtlib, oracle_mod, scene_dir, tmp_path):
+    """ray_b200 -r 5 -w 200 in.ray out.bmp (the reference's command line over the C++ RayTracer
+    mirror class) writes the frame the reference's traceImage produces."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "cs378hgraphics_raytracer_b200", "ray_b200")
+    if not os.path.exists(exe):
+        pytest.skip("ray_b200 not built")
+    path = scene_dir / "prims_mixed.ray"
+    out = tmp_path / "o.bmp"
+    r = subprocess.run([exe, "-r", "5", "-w", "200", str(path), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    raw = out.read_bytes()
+    w = int.from_bytes(raw[18:22], "little")
+    h = int.from_bytes(raw[22:26], "little")
+    row = (w * 3 + 3) // 4 * 4
+    px = np.frombuffer(raw[54:54 + row * h], dtype=np.uint8).reshape(h, row)[:, :w * 3].reshape(h, w, 3)[:, :, ::-1]
+    orc = oracle_mod.Oracle(str(path))
+    assert h == oracle_mod.frame_height(200, orc.aspect)
+    ref_img, _, _ = orc.render(rtlib.Params.default(depth=5), w, h)
+    d = oracle_mod.image_diff(ref_img, px)
+    assert d["within1"] >= TOL_WITHIN1, d

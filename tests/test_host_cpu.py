@@ -150,3 +150,17 @@ def test_device_code_on_host_frame_and_ray_counts(rtlib, oracle_mod, hostsim, sc
     assert d["within1"] >= 0.999, d
     assert (st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays) == \
         (ref_st.camera_rays, ref_st.reflection_rays, ref_st.refraction_rays, ref_st.shadow_rays)
+
+
+def test_cli_fails_loudly_without_gpu(scene_dir, tmp_path):
+    """ray_b200 (C++ RayTracer mirror + the reference's command line) has no CPU path either."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    exe = os.path.join(ROOT, "cs378hgraphics_raytracer_b200", "ray_b200")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "cs378hgraphics_raytracer_b200", "csrc"), "cli"])
+    r = subprocess.run([exe, "-r", "5", "-w", "64", str(scene_dir / "prims_mixed.ray"), str(tmp_path / "o.bmp")], capture_output=True, text=True)
+    assert r.returncode == 1
+    assert "no CUDA device" in r.stderr
+    assert not (tmp_path / "o.bmp").exists()

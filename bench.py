@@ -174,6 +174,15 @@ def load_cost_model(key):
     return None
 
 
+def load_dram_traffic(key, kind):
+    """DRAM bytes of one launch of the stage kernel from the committed `ncu --set full` capture."""
+    p = os.path.join(ROOT, "profiles", "dram_traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return (json.load(f).get(key) or {}).get(kind)
+    return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -335,7 +344,7 @@ def run_b200(args, key, wl, rank, world, local_rank):
             alg_bytes = ck["bytes_per_ray"] * n_rays
             ach = alg_bytes / (k_ms * 1e-3) / 1e9
             out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                               "traffic": (cm.get("dram_traffic") or {}).get(kind), "peak_source": peak_src, "kernel": kernel,
+                               "traffic": load_dram_traffic(key, kind), "peak_source": peak_src, "kernel": kernel,
                                "kernel_ms_per_launch": k_ms / max(k_n, 1), "launches_per_step": k_n / args.steps,
                                "algorithmic_bytes_per_launch": alg_bytes / max(k_n, 1), "bytes_per_ray": ck["bytes_per_ray"],
                                "note": "the walk is FP64-latency bound, not bandwidth bound: the scene is L2 resident (DESIGN.md, roofline)",

@@ -67,9 +67,11 @@ struct HitQueue {
 struct WaveCounters {
 	unsigned long long stats[8]; // camera, reflection, refraction, shadow rays, overflow flag, heavy rays
 	unsigned long long n_children;
-	unsigned long long n_shadow;
 	unsigned long long n_heavy;      // rays of this round that exhausted the node budget
 	unsigned long long heavy_cursor; // next heavy ray to be taken by a warp
+	unsigned long long pad;
+	unsigned long long n_shadow[2];  // per round parity: the shadow rays of round r are still being
+	                                 // walked (second stream) while round r+1 fills the other queue
 };
 
 // One entry per lane with pred set, appended to a queue shared by the whole grid: one atomic per
@@ -181,7 +183,7 @@ __global__ void __launch_bounds__(32 * RT_COOP_WARPS) k_wave_closest_heavy(const
 
 // ---- stage 2: RayTracer::traceRay's body --------------------------------------------------------
 __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_shade(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue Q, long long base, long long m, const HitQueue H,
-                                                                 const RayQueue Nxt, const RayQueue SQ, WaveCounters* cnt)
+                                                                 const RayQueue Nxt, const RayQueue SQ, int parity, WaveCounters* cnt)
 {
 	const unsigned lane = threadIdx.x & 31;
 	const unsigned lt_mask = (1u << lane) - 1u;
@@ -241,7 +243,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_shade(const __grid_con
 	// that neighbouring entries of the shadow queue aim at the same light
 	if (__any_sync(0xffffffffu, lit)) {
 		for (int li = 0; li < S.n_lights; li++) {
-			const long long s = wave_reserve(lit, lt_mask, &cnt->n_shadow);
+			const long long s = wave_reserve(lit, lt_mask, &cnt->n_shadow[parity]);
 			if (s >= 0) {
 				n_shadow++;
 				if (s >= SQ.cap) { overflow = 1; continue; }
@@ -275,10 +277,10 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_shade(const __grid_con
 #ifndef RT_SHADOW_MINB
 #define RT_SHADOW_MINB 10 // 96 registers
 #endif
-__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, const WaveCounters* cnt)
+__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt)
 {
 	const long long k = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
-	long long n = (long long)cnt->n_shadow;
+	long long n = (long long)cnt->n_shadow[parity];
 	if (n > SQ.cap) n = SQ.cap;
 	if (k >= n) return;
 	const d3 ro = SQ.load_v(0, k), rd = SQ.load_v(3, k);

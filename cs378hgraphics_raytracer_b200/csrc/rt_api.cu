@@ -40,6 +40,9 @@ struct rt_ctx {
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
 	unsigned long long* pinned = nullptr;  // round counters read back by the host
 	cudaEvent_t ev_round = nullptr;
+	cudaStream_t stream2 = nullptr;        // shadow rays of round r overlap round r+1's closest-hit work
+	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
+	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
 	unsigned long long rounds = 0;
 	// optional per-stage timing
 	bool profile = false;
@@ -52,7 +55,7 @@ struct rt_ctx {
 namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
-       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY,
+       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_SQ2_D, B_SQ2_I,
        B_ARENA, B_SNODES2, B_MNODES2, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_COUNT };
 static_assert(B_COUNT <= 48, "rt_ctx::buf too small");
 
@@ -132,14 +135,15 @@ cudaEvent_t next_event(rt_ctx* ctx)
 	return ctx->ev_pool[ctx->ev_used++];
 }
 // STAGE(id, launch): the launch, bracketed by events when profiling is on
-#define STAGE(id, ...)                                                        \
+#define STAGE_ON(strm, id, ...)                                               \
 	do {                                                                      \
 		cudaEvent_t a_ = nullptr, b_ = nullptr;                               \
-		if (ctx->profile) { a_ = next_event(ctx); b_ = next_event(ctx); cudaEventRecord(a_, ctx->stream); } \
+		if (ctx->profile) { a_ = next_event(ctx); b_ = next_event(ctx); cudaEventRecord(a_, strm); } \
 		__VA_ARGS__;                                                          \
 		ctx->launches++;                                                      \
-		if (ctx->profile) { cudaEventRecord(b_, ctx->stream); ctx->spans.push_back({id, a_, b_}); } \
+		if (ctx->profile) { cudaEventRecord(b_, strm); ctx->spans.push_back({id, a_, b_}); } \
 	} while (0)
+#define STAGE(id, ...) STAGE_ON(ctx->stream, id, __VA_ARGS__)
 
 // The trace loop over n_slots primary-ray slots as a streaming wavefront (device/rt_wave.cuh).
 rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
@@ -151,11 +155,15 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	const long long fit = ((A.n_slots + 1023) / 1024) * 1024;
 	if (W > fit) W = fit;
 	rt_status st;
-	RayQueue cur, nxt, sq, sp;
+	RayQueue cur, nxt, sq[2], sp;
 	sp.d = nullptr; sp.i = nullptr; sp.cap = 0; sp.nd = 12;
 	if ((st = make_queue(ctx, B_WQ0_D, B_WQ0_I, 2 * W, 12, cur)) != RT_OK) return st;
 	if ((st = make_queue(ctx, B_WQ1_D, B_WQ1_I, 2 * W, 12, nxt)) != RT_OK) return st;
-	if ((st = make_queue(ctx, B_SQ_D, B_SQ_I, W * (L > 0 ? L : 1), 9, sq)) != RT_OK) return st;
+	if ((st = make_queue(ctx, B_SQ_D, B_SQ_I, W * (L > 0 ? L : 1), 9, sq[0])) != RT_OK) return st;
+	if ((st = make_queue(ctx, B_SQ2_D, B_SQ2_I, W * (L > 0 ? L : 1), 9, sq[1])) != RT_OK) return st;
+	cudaStream_t sstream = ctx->overlap ? ctx->stream2 : ctx->stream;
+	bool shadow_pending[2] = {false, false};
+	long long round = 0;
 	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_WH_OF, (size_t)W * sizeof(int2))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_HEAVY, (size_t)W * sizeof(int))) != RT_OK) return st;
@@ -198,16 +206,26 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 			m = cur_n;
 		}
 		if (m == 0) break;
+		const int par = (int)(round & 1);
+		// this parity's shadow queue is free once the shadow kernel of two rounds ago is done
+		if (shadow_pending[par] && ctx->overlap) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_shadow[par], 0));
+		shadow_pending[par] = false;
 		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
+		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt));
 		if (ctx->walk_budget > 0)
 			STAGE(RT_STAGE_COOP, k_wave_closest_heavy<<<ctx->sm_count * 4, 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt));
-		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq, cnt));
-		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		if (L > 0) {
+			if (ctx->overlap) {
+				CK(cudaEventRecord(ctx->ev_shade[par], ctx->stream));
+				CK(cudaStreamWaitEvent(sstream, ctx->ev_shade[par], 0));
+			}
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
-			STAGE(RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, A, sq, cnt));
+			STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt));
+			if (ctx->overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
 		CK(cudaEventSynchronize(ctx->ev_round)); // the host plans the next round while the shadow rays run
@@ -216,12 +234,16 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		// the node budget follows the scene: if more than ~1.5 % of a round's rays ran out of it, the
 		// ordinary walk of this scene is simply longer (deep scene-level trees) - double it.  Either
 		// path gives the same hit, so this only moves work between the two kernels.
-		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)ctx->pinned[2] * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
+		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)ctx->pinned[1] * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
+		round++;
 		const RayQueue tmp = cur;
 		cur = nxt;
 		nxt = tmp;
 		ctx->rounds++;
 	}
+	// everything that follows on the main stream (resolve kernels, the frame copy) needs the last shadow rays
+	for (int par = 0; par < 2; par++)
+		if (shadow_pending[par]) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_shadow[par], 0));
 	return RT_OK;
 }
 
@@ -294,6 +316,9 @@ rt_status rt_create(int device, rt_ctx** out)
 	cudaEventCreate(&ctx->ev0);
 	cudaEventCreate(&ctx->ev1);
 	cudaEventCreateWithFlags(&ctx->ev_round, cudaEventDisableTiming);
+	cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
+	for (int k = 0; k < 2; k++) { cudaEventCreateWithFlags(&ctx->ev_shade[k], cudaEventDisableTiming); cudaEventCreateWithFlags(&ctx->ev_shadow[k], cudaEventDisableTiming); }
+	if (const char* e = getenv("RT_B200_OVERLAP")) ctx->overlap = atoi(e) != 0;
 	if (cudaMallocHost((void**)&ctx->pinned, 64) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	if (const char* e = getenv("RT_B200_WAVE")) { const long long v = atoll(e); if (v >= 1024) ctx->wave_width = (v + 1023) / 1024 * 1024; }
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
@@ -320,6 +345,8 @@ void rt_destroy(rt_ctx* ctx)
 	for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
 	if (ctx->pinned) cudaFreeHost(ctx->pinned);
 	if (ctx->ev_round) cudaEventDestroy(ctx->ev_round);
+	for (int k = 0; k < 2; k++) { if (ctx->ev_shade[k]) cudaEventDestroy(ctx->ev_shade[k]); if (ctx->ev_shadow[k]) cudaEventDestroy(ctx->ev_shadow[k]); }
+	if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);

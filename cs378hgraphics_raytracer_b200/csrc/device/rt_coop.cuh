@@ -39,7 +39,7 @@ __device__ __forceinline__ double warp_min(double v)
 // Trimesh::intersectLocal (trimesh.cpp:79-95) over the mesh's tree by the whole warp.
 // o, d, I: the ray in the mesh's object space (the same in every lane); lim: object-space limit.
 // On return have / best_t / best_pos are warp-uniform.
-__device__ __noinline__ void coop_mesh(const DTree& T, const DNode2* nodes, const DTri* tris, const d3& o, const d3& d, const RayInv& I, double lim,
+__device__ __noinline__ void coop_mesh(const DTree& T, const DNode2* nodes, const DNode2f* nodesf, const DTri* tris, const d3& o, const d3& d, const RayInv& I, const RayF& F, double lim,
                                        CoopStack& K, bool& have, double& best_t, int& best_pos)
 {
 	const unsigned lane = threadIdx.x & 31;
@@ -70,10 +70,10 @@ __device__ __noinline__ void coop_mesh(const DTree& T, const DNode2* nodes, cons
 		double ce0 = 0.0, ce1 = 0.0;
 		if (ref != RT_REF_NONE) {
 			if (ref >= 0) {
-				const DNode2& nd = nodes[ref];
+				const DNode2f& nd = nodesf[ref];
 				double e0, e1;
-				bool h0 = box_hit(nd.lo0, nd.hi0, o, d, I, e0);
-				bool h1 = box_hit(nd.lo1, nd.hi1, o, d, I, e1);
+				bool h0, h1;
+				box2_hit(nd, nodes[ref], o, d, I, F, h0, h1, e0, e1);
 				h0 = h0 && !(e0 > lim);
 				h1 = h1 && !(e1 > lim);
 				if (h0 && h1) {
@@ -132,7 +132,8 @@ __device__ __forceinline__ void coop_closest(const DScene& S, const d3& ow, cons
 	int stk[RT_STACK];
 	double stke[RT_STACK];
 	RayInv I;
-	make_inv(I, dw, S.scene_slack);
+	RayF F;
+	make_inv(I, F, ow, dw, S.scene_slack, S.scene_slack * 1e9);
 	double lim = RT_T_INF;
 	double e;
 	if (!box_hit(S.stree.lo, S.stree.hi, ow, dw, I, e)) return;
@@ -141,10 +142,10 @@ __device__ __forceinline__ void coop_closest(const DScene& S, const d3& ow, cons
 	for (;;) {
 #pragma unroll 1
 		while (cur >= 0) {
-			const DNode2& n = S.snodes2[cur];
+			const DNode2f& n = S.snodes2f[cur];
 			double e0, e1;
-			bool h0 = box_hit(n.lo0, n.hi0, ow, dw, I, e0);
-			bool h1 = box_hit(n.lo1, n.hi1, ow, dw, I, e1);
+			bool h0, h1;
+			box2_hit(n, S.snodes2[cur], ow, dw, I, F, h0, h1, e0, e1);
 			h0 = h0 && !(e0 > lim);
 			h1 = h1 && !(e1 > lim);
 			const int c0 = n.c0, c1 = n.c1;
@@ -174,11 +175,12 @@ __device__ __forceinline__ void coop_closest(const DScene& S, const d3& ow, cons
 					const DTree& T = S.mtrees[ob.mesh];
 					const int item_off = (int)S.meshes[ob.mesh].item_off;
 					RayInv Il;
-					make_inv(Il, L.d, S.mesh_slack[ob.mesh]);
+					RayF Fl;
+					make_inv(Il, Fl, L.o, L.d, S.mesh_slack[ob.mesh], S.mesh_slack[ob.mesh] * 1e9);
 					bool have;
 					double bt;
 					int bp;
-					coop_mesh(T, S.mnodes2 + T.node_off, S.tris + item_off, L.o, L.d, Il, lim_to_local(lim, L.len), K, have, bt, bp);
+					coop_mesh(T, S.mnodes2 + T.node_off, S.mnodes2f + T.node_off, S.tris + item_off, L.o, L.d, Il, Fl, lim_to_local(lim, L.len), K, have, bt, bp);
 					if (have) {
 						const double t = bt / L.len;
 						if (!C.have || t < C.best_t || (t == C.best_t && rank < C.best_rank)) {

@@ -11,6 +11,7 @@ namespace rtd {
 
 struct Derived {
 	std::vector<DNode2> snodes2, mnodes2;
+	std::vector<DNode2f> snodes2f, mnodes2f;
 	DTree stree;
 	std::vector<DTree> mtrees;
 	std::vector<DTri> tris;
@@ -60,6 +61,19 @@ inline void build_nodes2(const rt_node* n, uint64_t cnt, std::vector<DNode2>& ou
 	}
 }
 
+inline void nodes_to_float(const std::vector<DNode2>& in, std::vector<DNode2f>& out)
+{
+	out.resize(in.size());
+	for (size_t k = 0; k < in.size(); k++) {
+		const DNode2& a = in[k];
+		DNode2f& f = out[k];
+		for (int c = 0; c < 3; c++) { f.lo0[c] = (float)a.lo0[c]; f.hi0[c] = (float)a.hi0[c]; f.lo1[c] = (float)a.lo1[c]; f.hi1[c] = (float)a.hi1[c]; }
+		f.c0 = a.c0;
+		f.c1 = a.c1;
+		f.pad[0] = f.pad[1] = 0;
+	}
+}
+
 inline double box_extent(const rt_node& n)
 {
 	double m = 1.0;
@@ -103,6 +117,8 @@ inline void derive(const rt::ArenaView& A, Derived& D)
 	D.scene_slack = 1e-9 * box_extent(snodes[0]);
 	build_nodes2(snodes, A.count(RT_SEC_SCENE_NODES), D.snodes2, D.stree);
 	D.max_scene_depth = tree_depth(snodes, A.count(RT_SEC_SCENE_NODES));
+	nodes_to_float(D.snodes2, D.snodes2f);
+	nodes_to_float(D.mnodes2, D.mnodes2f);
 }
 
 } // namespace rtd

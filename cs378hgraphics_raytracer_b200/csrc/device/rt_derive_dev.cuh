@@ -63,6 +63,21 @@ __global__ void __launch_bounds__(256) k_derive_nodes2(const rt_node* n, long lo
 	out[pre[k]] = d;
 }
 
+// float image of the wide nodes (round to nearest, like the host's (float) casts)
+__global__ void __launch_bounds__(256) k_derive_nodes2f(const DNode2* in, long long cnt, DNode2f* out)
+{
+	const long long k = (long long)blockIdx.x * 256 + threadIdx.x;
+	if (k >= cnt) return;
+	const DNode2& a = in[k];
+	DNode2f f;
+#pragma unroll
+	for (int c = 0; c < 3; c++) { f.lo0[c] = (float)a.lo0[c]; f.hi0[c] = (float)a.hi0[c]; f.lo1[c] = (float)a.lo1[c]; f.hi1[c] = (float)a.hi1[c]; }
+	f.c0 = a.c0;
+	f.c1 = a.c1;
+	f.pad[0] = f.pad[1] = 0;
+	out[k] = f;
+}
+
 __device__ __forceinline__ double dev_box_extent(const rt_node& n)
 {
 	double m = 1.0;

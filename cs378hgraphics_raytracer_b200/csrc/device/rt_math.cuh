@@ -94,8 +94,36 @@ struct RayInv {
 	unsigned span; // width of the exponent window of `a` served by the FMA path: 1201, or 0 when
 	               // some |d| lies outside [2^-300, 2^300] (every quotient is then a real division)
 };
+// Single-precision image of the ray for the box PRE-test (rt_prims.cuh: box2_hit).  With node boxes
+// rounded to float, every slab quotient computed in float differs from the reference's double
+// quotient by less than  4u|q| + 1.1u (E + |o_i|) |y_i|  (u = 2^-24, E = largest |coordinate| of the
+// tree's root box).  amax carries the absolute part with a 3.6x margin; it is +inf when a direction
+// component is zero or anything is out of float range, which makes every box "ambiguous" and hands
+// the decision to the double-precision test.
+RT_HD void make_inv(RayInv& I, const d3& d, double slack);
+struct RayF {
+	float ox, oy, oz;
+	float yx, yy, yz;
+	float amax;
+};
 RT_HD bool div_range_ok(double d) { const double a = fabs(d); return d == 0.0 || (a >= 0x1p-300 && a <= 0x1p300); }
-RT_COLD void make_inv(RayInv& I, const d3& d, double slack)
+RT_HD void make_rayf(RayF& F, const d3& o, const d3& d, const d3& y, double extent)
+{
+	F.ox = (float)o.x; F.oy = (float)o.y; F.oz = (float)o.z;
+	F.yx = (float)y.x; F.yy = (float)y.y; F.yz = (float)y.z;
+	const double ax = (extent + fabs(o.x)) * fabs(y.x), ay = (extent + fabs(o.y)) * fabs(y.y), az = (extent + fabs(o.z)) * fabs(y.z);
+	double m = ax > ay ? ax : ay;
+	m = az > m ? az : m;
+	const bool ok = d.x != 0.0 && d.y != 0.0 && d.z != 0.0 && fabs(y.x) <= 1e15 && fabs(y.y) <= 1e15 && fabs(y.z) <= 1e15 &&
+	                extent + fabs(o.x) <= 1e15 && extent + fabs(o.y) <= 1e15 && extent + fabs(o.z) <= 1e15;
+	F.amax = ok ? (float)(m * 0x1p-22) * 1.0001f + 1e-30f : INFINITY; // m 2^-22 = 4u m, rounded up
+}
+RT_COLD void make_inv(RayInv& I, RayF& F, const d3& o, const d3& d, double slack, double extent)
+{
+	make_inv(I, d, slack);
+	make_rayf(F, o, d, I.y, extent);
+}
+RT_HD void make_inv(RayInv& I, const d3& d, double slack)
 {
 	I.y = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
 	const d3 sl = mk3(slack * fabs(I.y.x), slack * fabs(I.y.y), slack * fabs(I.y.z));

@@ -68,6 +68,30 @@ RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3
 	return box_hit_exact(bmin, bmax, o, d, I, entry);
 }
 
+// Both children of a node at once, float first.  Per child the float test ends in one of three
+// states: certainly hit, certainly missed (by the margins derived at RayF), or ambiguous - and only
+// an ambiguous child reads its double box and takes box_hit.  e0/e1 are conservative entry
+// distances (never above the exact tMin minus the pruning slack).
+RT_HD void box2_hit(const DNode2f& nf, const DNode2& n, const d3& o, const d3& d, const RayInv& I, const RayF& F, bool& h0, bool& h1, double& e0, double& e1)
+{
+#define RT_BOXF(LO, HI, H, E, LO64, HI64)                                                        \
+	{                                                                                            \
+		const float qx1 = (LO[0] - F.ox) * F.yx, qx2 = (HI[0] - F.ox) * F.yx;                    \
+		const float qy1 = (LO[1] - F.oy) * F.yy, qy2 = (HI[1] - F.oy) * F.yy;                    \
+		const float qz1 = (LO[2] - F.oz) * F.yz, qz2 = (HI[2] - F.oz) * F.yz;                    \
+		const float tn = fmaxf(fmaxf(fminf(qx1, qx2), fminf(qy1, qy2)), fminf(qz1, qz2));        \
+		const float tf = fminf(fminf(fmaxf(qx1, qx2), fmaxf(qy1, qy2)), fmaxf(qz1, qz2));        \
+		const float s = 2.0f * F.amax + 0x1p-20f * (fabsf(tn) + fabsf(tf));                      \
+		const float gap = tf - tn;                                                               \
+		if (gap < -s || tf + s < (float)RT_RAY_EPSILON) { H = false; E = 0.0; }                  \
+		else if (gap > s && tf - s > (float)RT_RAY_EPSILON * 1.0001f) { H = true; E = (double)(tn - s) - I.slmax; } \
+		else H = box_hit(LO64, HI64, o, d, I, E);                                                \
+	}
+	RT_BOXF(nf.lo0, nf.hi0, h0, e0, n.lo0, n.hi0)
+	RT_BOXF(nf.lo1, nf.hi1, h1, e1, n.lo1, n.hi1)
+#undef RT_BOXF
+}
+
 // What a primitive's intersectLocal leaves in the isect (object space).
 struct LocalHit {
 	double t;

@@ -27,6 +27,15 @@ struct alignas(128) DNode2 {
 	int32_t c0, c1;
 	int32_t pad[6];
 };
+// The same node with the boxes rounded to float (round to nearest): what the walk reads first.
+// Half the bytes per step; the double node is fetched only for a child whose float test is
+// ambiguous (rt_prims.cuh: box2_hit).
+struct alignas(64) DNode2f {
+	float lo0[3], hi0[3];
+	float lo1[3], hi1[3];
+	int32_t c0, c1;
+	int32_t pad[2];
+};
 #define RT_REF_MESH_EXIT ((int32_t)0x80000000)
 #define RT_REF_NONE ((int32_t)0x80000001)
 RT_HD int32_t leaf_ref(int32_t first, int32_t count) { return -(1 + ((first << 2) | count)); }
@@ -44,6 +53,8 @@ struct DScene {
 	const DNode2* snodes2;
 	DTree stree;
 	const DNode2* mnodes2;
+	const DNode2f* snodes2f; // float images, same indexing
+	const DNode2f* mnodes2f;
 	const DTree* mtrees; // per mesh
 	const rt_node* snodes;
 	const int32_t* sitems;

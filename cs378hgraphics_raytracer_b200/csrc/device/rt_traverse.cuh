@@ -191,8 +191,10 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 	// current space (world at level 0, the mesh's object space at level 1)
 	d3 o = ow, d = dw;
 	RayInv I;
-	make_inv(I, d, prune ? S.scene_slack : 0.0);
+	RayF F;
+	make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
 	const DNode2* nodes = S.snodes2;
+	const DNode2f* nodesf = S.snodes2f;
 	const DTri* tris = S.tris;
 	int level = 0;
 	double lim = mode == TRAV_CLOSEST ? RT_T_INF : B.cut;
@@ -212,14 +214,14 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 		// ---- 1. internal nodes: test both children, go near, push far ---------------------------
 #pragma unroll 1
 		while (cur >= 0) {
-			const DNode2& n = nodes[cur];
+			const DNode2f& nf = nodesf[cur];
 			RT_CNT(nodes, mode);
 			if (budget > 0 && --budget == 0) return false;
 			double e0, e1;
-			bool h0 = box_hit(n.lo0, n.hi0, o, d, I, e0);
-			bool h1 = box_hit(n.lo1, n.hi1, o, d, I, e1);
+			bool h0, h1;
+			box2_hit(nf, nodes[cur], o, d, I, F, h0, h1, e0, e1);
 			if (prune) { h0 = h0 && !(e0 > lim); h1 = h1 && !(e1 > lim); }
-			const int c0 = n.c0, c1 = n.c1;
+			const int c0 = nf.c0, c1 = nf.c1;
 			if (h0 && h1) {
 				const bool swap = prune && e1 < e0;
 				stk[sp] = swap ? c0 : c1;
@@ -284,9 +286,10 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 						V.best_pos = 0x7fffffff;
 						tris = S.tris + V.item_off;
 						nodes = S.mnodes2 + T.node_off;
+						nodesf = S.mnodes2f + T.node_off;
 						o = L.o;
 						d = L.d;
-						make_inv(I, d, prune ? S.mesh_slack[ob.mesh] : 0.0);
+						make_inv(I, F, o, d, prune ? S.mesh_slack[ob.mesh] : 0.0, S.mesh_slack[ob.mesh] * 1e9);
 						level = 1;
 						lim = lim_to_local(lim, V.len);
 						double er;
@@ -324,8 +327,9 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 					}
 					o = ow;
 					d = dw;
-					make_inv(I, d, prune ? S.scene_slack : 0.0);
+					make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
 					nodes = S.snodes2;
+					nodesf = S.snodes2f;
 					level = 0;
 					lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : B.cut;
 					continue;

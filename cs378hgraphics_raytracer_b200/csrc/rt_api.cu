@@ -56,7 +56,7 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_SQ2_D, B_SQ2_I,
-       B_ARENA, B_SNODES2, B_MNODES2, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_COUNT };
+       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_COUNT };
 static_assert(B_COUNT <= 48, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -161,7 +161,9 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if ((st = make_queue(ctx, B_WQ1_D, B_WQ1_I, 2 * W, 12, nxt)) != RT_OK) return st;
 	if ((st = make_queue(ctx, B_SQ_D, B_SQ_I, W * (L > 0 ? L : 1), 9, sq[0])) != RT_OK) return st;
 	if ((st = make_queue(ctx, B_SQ2_D, B_SQ2_I, W * (L > 0 ? L : 1), 9, sq[1])) != RT_OK) return st;
-	cudaStream_t sstream = ctx->overlap ? ctx->stream2 : ctx->stream;
+	// per-stage profiling wants clean kernel times: no overlap then
+	const bool overlap = ctx->overlap && !ctx->profile;
+	cudaStream_t sstream = overlap ? ctx->stream2 : ctx->stream;
 	bool shadow_pending[2] = {false, false};
 	long long round = 0;
 	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
@@ -208,7 +210,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		if (m == 0) break;
 		const int par = (int)(round & 1);
 		// this parity's shadow queue is free once the shadow kernel of two rounds ago is done
-		if (shadow_pending[par] && ctx->overlap) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_shadow[par], 0));
+		if (shadow_pending[par] && overlap) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_shadow[par], 0));
 		shadow_pending[par] = false;
 		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
 		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
@@ -219,13 +221,13 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		if (L > 0) {
-			if (ctx->overlap) {
+			if (overlap) {
 				CK(cudaEventRecord(ctx->ev_shade[par], ctx->stream));
 				CK(cudaStreamWaitEvent(sstream, ctx->ev_shade[par], 0));
 			}
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
 			STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt));
-			if (ctx->overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
+			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
 		CK(cudaEventSynchronize(ctx->ev_round)); // the host plans the next round while the shadow rays run
@@ -366,10 +368,11 @@ rt_status rt_set_profiling(rt_ctx* ctx, int on)
 // nodes: cnt reference nodes in pre-order (n_mesh trees back to back, or the scene tree when
 // n_mesh == 0).  *max_depth receives the deepest node's depth (bit 31: deeper than 128).
 static rt_status derive_trees(rt_ctx* ctx, const rt_node* nodes, long long cnt, const rt_mesh* ms, int n_mesh, long long scene_items,
-                              int b_nodes2, int b_pre, unsigned* err, unsigned* max_depth)
+                              int b_nodes2, int b_nodes2f, int b_pre, unsigned* err, unsigned* max_depth)
 {
 	rt_status st;
 	if ((st = ensure(ctx, b_nodes2, (size_t)(cnt > 0 ? cnt : 1) * sizeof(DNode2))) != RT_OK) return st;
+	if ((st = ensure(ctx, b_nodes2f, (size_t)(cnt > 0 ? cnt : 1) * sizeof(DNode2f))) != RT_OK) return st;
 	if ((st = ensure(ctx, b_pre, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_TMP_A, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_TMP_B, (size_t)(cnt + 1) * sizeof(int))) != RT_OK) return st;
@@ -384,7 +387,10 @@ static rt_status derive_trees(rt_ctx* ctx, const rt_node* nodes, long long cnt, 
 	CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flag, pre, (int)cnt, ctx->stream));
 	if ((st = ensure(ctx, B_CUBTMP, tmp_bytes)) != RT_OK) return st;
 	CK(cub::DeviceScan::ExclusiveSum(ctx->buf[B_CUBTMP], tmp_bytes, flag, pre, (int)cnt, ctx->stream));
+	// entries of internal nodes only are written; clear the rest so that the float image below reads defined bytes
+	CK(cudaMemsetAsync(ctx->buf[b_nodes2], 0, (size_t)cnt * sizeof(DNode2), ctx->stream));
 	k_derive_nodes2<<<g, 256, 0, ctx->stream>>>(nodes, cnt, pre, ms, n_mesh, scene_items, (DNode2*)ctx->buf[b_nodes2], err);
+	k_derive_nodes2f<<<g, 256, 0, ctx->stream>>>((const DNode2*)ctx->buf[b_nodes2], cnt, (DNode2f*)ctx->buf[b_nodes2f]);
 	// depth: parent links + 7 rounds of pointer jumping (covers depth <= 128)
 	int* anc[2] = {(int*)ctx->buf[B_TMP_A], (int*)ctx->buf[B_TMP_C]};
 	int* dist[2] = {(int*)ctx->buf[B_TMP_B], (int*)ctx->buf[B_TMP_D]};
@@ -448,8 +454,8 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 #undef SEC
 	unsigned* flags = (unsigned*)((unsigned long long*)ctx->buf[B_SMALL] + 28); // err, scene depth, mesh depth
 	CK(cudaMemsetAsync(flags, 0, 3 * sizeof(unsigned), ctx->stream));
-	if ((st = derive_trees(ctx, S.snodes, n_snodes, nullptr, 0, n_sitems, B_SNODES2, B_PRE_S, flags, flags + 1)) != RT_OK) return st;
-	if ((st = derive_trees(ctx, S.mnodes, n_mnodes, S.meshes, n_mesh, 0, B_MNODES2, B_PRE_M, flags, flags + 2)) != RT_OK) return st;
+	if ((st = derive_trees(ctx, S.snodes, n_snodes, nullptr, 0, n_sitems, B_SNODES2, B_SNODES2F, B_PRE_S, flags, flags + 1)) != RT_OK) return st;
+	if ((st = derive_trees(ctx, S.mnodes, n_mnodes, S.meshes, n_mesh, 0, B_MNODES2, B_MNODES2F, B_PRE_M, flags, flags + 2)) != RT_OK) return st;
 	if ((st = ensure(ctx, B_MTREES, (size_t)(n_mesh > 0 ? n_mesh : 1) * sizeof(DTree))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_MSLACK, (size_t)(n_mesh > 0 ? n_mesh : 1) * sizeof(double))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_TRIS, (size_t)(n_mitems > 0 ? n_mitems : 1) * sizeof(DTri))) != RT_OK) return st;
@@ -466,6 +472,8 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	CK(cudaGetLastError());
 	S.snodes2 = (const DNode2*)ctx->buf[B_SNODES2];
 	S.mnodes2 = (const DNode2*)ctx->buf[B_MNODES2];
+	S.snodes2f = (const DNode2f*)ctx->buf[B_SNODES2F];
+	S.mnodes2f = (const DNode2f*)ctx->buf[B_MNODES2F];
 	S.mtrees = (const DTree*)ctx->buf[B_MTREES];
 	S.mesh_slack = (const double*)ctx->buf[B_MSLACK];
 	S.tris = (const DTri*)ctx->buf[B_TRIS];
@@ -511,6 +519,8 @@ rt_status rt_selftest_derive(rt_ctx* ctx, const void* arena, size_t bytes, unsig
 	rt_status st;
 	if ((st = cmp(ctx->S.snodes2, D.snodes2.data(), D.snodes2.size() * sizeof(DNode2))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.mnodes2, D.mnodes2.data(), D.mnodes2.size() * sizeof(DNode2))) != RT_OK) return st;
+	if ((st = cmp(ctx->S.snodes2f, D.snodes2f.data(), D.snodes2f.size() * sizeof(DNode2f))) != RT_OK) return st;
+	if ((st = cmp(ctx->S.mnodes2f, D.mnodes2f.data(), D.mnodes2f.size() * sizeof(DNode2f))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.mtrees, D.mtrees.data(), D.mtrees.size() * sizeof(DTree))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.tris, D.tris.data(), D.tris.size() * sizeof(DTri))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.mesh_slack, D.mesh_slack.data(), D.mesh_slack.size() * sizeof(double))) != RT_OK) return st;

@@ -144,18 +144,6 @@ struct Region {
 	int level;
 };
 
-// hammersley(k, N) (reference util.cpp:3-11): radical inverse base 2; the second coordinate is
-// always 0 because n has been shifted down to 0 by the time it is used.
-__device__ __forceinline__ double radical_inverse2(int n)
-{
-	double mul = 0.5, result = 0.0;
-	while (n > 0) {
-		result += (n % 2) ? mul : 0;
-		n /= 2;
-		mul /= 2.0;
-	}
-	return result;
-}
 
 __global__ void __launch_bounds__(256) k_adapt_init(const PoolArgs A, long long n_pix, Region* regions)
 {

@@ -156,6 +156,19 @@ RT_HD double div_by(double a, double d, double y, unsigned span)
 	return fma(r, y, q);
 }
 
+// hammersley(k, N) (reference util.cpp:3-11): radical inverse base 2; the second coordinate is
+// always 0 because n has been shifted down to 0 by the time it is used.
+RT_HD double radical_inverse2(int n)
+{
+	double mul = 0.5, result = 0.0;
+	while (n > 0) {
+		result += (n % 2) ? mul : 0;
+		n /= 2;
+		mul /= 2.0;
+	}
+	return result;
+}
+
 #define RT_RAY_EPSILON 0.00000001
 #define RT_EPS32 (RT_RAY_EPSILON / 32)
 

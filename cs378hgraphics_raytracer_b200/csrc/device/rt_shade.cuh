@@ -65,6 +65,57 @@ RT_COLD void light_term(const rt_light& L, const MatEval& m, const d3& P, const 
 	term = (dattn * ld3(L.color)) * (d_comp + s_comp);
 }
 
+// ---- area and spot lights (reference scene/light.cpp:76-149, light.h:100-164) ----------------------
+// AreaLight::shadowAttenuation = (1 + sum over the valid samples i < softShadowRes of
+// srsAttenuation(pb, normalize(pick(i) - pb))) * (1 / (softShadowRes - 1)) - the sum starts at 1 and the
+// divisor is res - 1, as written.  Point and directional lights trace one ray.
+RT_HD bool light_is_area(const rt_light& L) { return L.type >= RT_LIGHT_AREA_RECT; }
+RT_HD int light_samples(const rt_light& L, const rt_params& prm) { return light_is_area(L) ? prm.soft_shadow_res : 1; }
+RT_HD double light_sample_weight(const rt_light& L, const rt_params& prm) { return light_is_area(L) ? 1.0 / (prm.soft_shadow_res - 1) : 1.0; }
+
+// SpotLight::validImpact(r, p) (light.cpp:148-150); true for the other kinds
+RT_COLD bool light_valid(const rt_light& L, const d3& p)
+{
+	if (L.type != RT_LIGHT_SPOT) return true;
+	const double PI_ = 3.1415926535897932384626433832795028841971;
+	const d3 ori = ld3(L.orientation), lpos = ld3(L.position);
+	const d3 dir = normalize(lpos - p);
+	return (dot(dir, ori) <= 0) && (dot(normalize(p - (lpos - L.offset * ori)), ori) > cos(PI_ / 4));
+}
+
+// i-th sample: AreaLightRect::pick (an offset in the light's plane that is NOT moved to the light's
+// position, light.cpp:101-104) or AreaLightCirc::pick (a ring of radius r/2, :113-136), then
+// SpotLight::validImpact(r, pb, lp).  false = the sample is skipped.
+RT_COLD bool light_sample(const rt_light& L, const rt_params& prm, int i, const d3& pb, d3& sdir)
+{
+	const double PI_ = 3.1415926535897932384626433832795028841971;
+	const d3 ori = ld3(L.orientation), lpos = ld3(L.position);
+	d3 lp;
+	if (L.type == RT_LIGHT_AREA_RECT) {
+		const double a = (radical_inverse2(i) - 0.5) * L.w, b = (0.0 - 0.5) * L.h;
+		const d3 u = ld3(L.u), v = ld3(L.v);
+		lp = mk3(u.x * a + v.x * b, u.y * a + v.y * b, u.z * a + v.z * b);
+	} else {
+		const double ang_rad = 2 * PI_ / prm.soft_shadow_res * i;
+		const double dist = 0.5 * L.radius;
+		const double x = cos(ang_rad) * dist, y = sin(ang_rad) * dist;
+		const d3 ab = mk3(fabs(ori.x), fabs(ori.y), fabs(ori.z));
+		d3 u;
+		if (ab.x < ab.y && ab.x < ab.z) u = mk3(0.0, -ori.z, ori.y);
+		else if (ab.y < ab.z) u = mk3(-ori.z, 0.0, ori.x);
+		else u = mk3(-ori.y, ori.x, 0.0);
+		u = normalize(u);
+		const d3 v = cross(ori, u);
+		lp = x * u + y * v + lpos;
+	}
+	if (L.type == RT_LIGHT_SPOT) {
+		const d3 dir = normalize(lpos - pb);
+		if (!((dot(dir, ori) <= 0) && (dot(normalize(pb - lp), ori) > cos(PI_ / 4)))) return false;
+	}
+	sdir = normalize(lp - pb);
+	return true;
+}
+
 // Material::shade with the shadow rays traced inline.  shadow_rays counts Scene::intersectList calls.
 RT_HD d3 shade(const DScene& S, const rt_params& prm, const MatEval& m, const d3& o, const d3& d, const Hit& h, unsigned& shadow_rays)
 {
@@ -74,8 +125,21 @@ RT_HD d3 shade(const DScene& S, const rt_params& prm, const MatEval& m, const d3
 		const rt_light& L = S.lights[li];
 		d3 term, pb, sdir;
 		light_term(L, m, P, h.N, d, term, pb, sdir);
-		shadow_rays++;
-		const d3 sattn = shadow_attenuation(S, L, pb, sdir, prm);
+		if (!light_is_area(L)) {
+			shadow_rays++;
+			const d3 sattn = shadow_attenuation(S, L, pb, sdir, prm);
+			out = out + sattn * term;
+			continue;
+		}
+		if (!light_valid(L, P)) continue; // shadowAttenuation returns 0 (light.cpp:78)
+		d3 sattn = mk3(1.0, 1.0, 1.0);
+		for (int i = 0; i < prm.soft_shadow_res; i++) {
+			d3 sd;
+			if (!light_sample(L, prm, i, pb, sd)) continue;
+			shadow_rays++;
+			sattn = sattn + shadow_attenuation(S, L, pb, sd, prm);
+		}
+		sattn = sattn * light_sample_weight(L, prm);
 		out = out + sattn * term;
 	}
 	return out;

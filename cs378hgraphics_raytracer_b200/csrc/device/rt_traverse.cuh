@@ -193,6 +193,8 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 	RayInv I;
 	RayF F;
 	make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
+	const RayInv Iw = I; // world-space copies, restored when the walk leaves a mesh
+	const RayF Fw = F;
 	const DNode2* nodes = S.snodes2;
 	const DNode2f* nodesf = S.snodes2f;
 	const DTri* tris = S.tris;
@@ -327,7 +329,8 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 					}
 					o = ow;
 					d = dw;
-					make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
+					I = Iw;
+					F = Fw;
 					nodes = S.snodes2;
 					nodesf = S.snodes2f;
 					level = 0;
@@ -376,11 +379,26 @@ struct ShadowState {
 	int point;
 };
 
+// AreaLightRect::impact / AreaLightCirc::impact (light.cpp:105-111, 138-146): where the ray meets the
+// light's plane; the disc variants answer (0,0,0) outside the radius
+RT_HD d3 area_impact(const rt_light& Lt, const d3& p, const d3& dir)
+{
+	const d3 ori = ld3(Lt.orientation), lpos = ld3(Lt.position);
+	double t = dot(ori, dir);
+	t = dot(lpos - p, ori) / t;
+	const d3 at = p + t * dir;
+	if (Lt.type == RT_LIGHT_AREA_RECT) return at;
+	if (dot(at - lpos, at - lpos) < (Lt.radius * Lt.radius)) return at;
+	return mk3(0.0, 0.0, 0.0);
+}
+
 RT_COLD void shadow_begin(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& pos)
 {
 	st.point = Lt.type != RT_LIGHT_DIRECTIONAL;
 	st.limit = RT_T_INF;
-	if (st.point) {
+	// area and spot lights: the limit check is against the ray's impact point on the light's plane
+	// (light.cpp:91-99), no distance bound is used for culling
+	if (Lt.type == RT_LIGHT_POINT) {
 		const double D = length(ld3(Lt.position) - pos);
 		st.limit = D * (1.0 + 1e-9) + 1e-9;
 	}
@@ -411,8 +429,10 @@ RT_COLD bool shadow_walk(ShadowState& st, SBuf& B, const rt_light& Lt, const d3&
 		const bool inside = (h.flags & 1) != 0;
 		st.cur = st.cur + t * dir;
 		// curr/next media: inside ? (m_in -> air) : (air -> m_in); overlapping-objects mode off
-		if (st.point) { // PointLight::sattnLimitCheck (light.cpp:65-71)
+		if (Lt.type == RT_LIGHT_POINT) { // PointLight::sattnLimitCheck (light.cpp:65-71)
 			if (dot(lpos - (st.cur + t * dir), dir) <= 0) return true;
+		} else if (st.point) { // AreaLight::sattnLimitCheck (light.cpp:91-99) with impact() of the Rect / Circ subclass
+			if (dot(area_impact(Lt, st.cur, dir) - (st.cur + t * dir), dir) <= 0) return true;
 		}
 		const bool next_trans = inside ? true : (h.flags & 2) != 0;
 		if (!next_trans) { st.sattn = mk3(0.0, 0.0, 0.0); return true; }

@@ -243,16 +243,42 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_shade(const __grid_con
 	// that neighbouring entries of the shadow queue aim at the same light
 	if (__any_sync(0xffffffffu, lit)) {
 		for (int li = 0; li < S.n_lights; li++) {
-			const long long s = wave_reserve(lit, lt_mask, &cnt->n_shadow[parity]);
-			if (s >= 0) {
-				n_shadow++;
-				if (s >= SQ.cap) { overflow = 1; continue; }
-				d3 term, pb, sdir;
-				light_term(S.lights[li], me, hitP, h.N, rd, term, pb, sdir);
-				SQ.store_v(0, s, pb);
-				SQ.store_v(3, s, sdir);
-				SQ.store_v(6, s, w * term);
-				SQ.store_meta(s, sample, li);
+			const rt_light& Lt = S.lights[li];
+			if (!light_is_area(Lt)) {
+				const long long s = wave_reserve(lit, lt_mask, &cnt->n_shadow[parity]);
+				if (s >= 0) {
+					n_shadow++;
+					if (s >= SQ.cap) { overflow = 1; continue; }
+					d3 term, pb, sdir;
+					light_term(Lt, me, hitP, h.N, rd, term, pb, sdir);
+					SQ.store_v(0, s, pb);
+					SQ.store_v(3, s, sdir);
+					SQ.store_v(6, s, w * term);
+					SQ.store_meta(s, sample, li);
+				}
+				continue;
+			}
+			// area / spot light: sattn = (1 + sum of the valid samples' attenuations) / (res - 1);
+			// the constant part goes to the sample now, every valid sample becomes a shadow ray
+			const bool lv = lit && light_valid(Lt, hitP);
+			d3 wt = mk3(0, 0, 0), pb = mk3(0, 0, 0), sdir = mk3(0, 0, 1);
+			if (lv) {
+				d3 term;
+				light_term(Lt, me, hitP, h.N, rd, term, pb, sdir);
+				wt = (w * term) * light_sample_weight(Lt, A.prm);
+				accumulate(A.accum, sample, wt);
+			}
+			for (int i = 0; i < A.prm.soft_shadow_res; i++) {
+				const bool ok = lv && light_sample(Lt, A.prm, i, pb, sdir);
+				const long long s = wave_reserve(ok, lt_mask, &cnt->n_shadow[parity]);
+				if (s >= 0) {
+					n_shadow++;
+					if (s >= SQ.cap) { overflow = 1; continue; }
+					SQ.store_v(0, s, pb);
+					SQ.store_v(3, s, sdir);
+					SQ.store_v(6, s, wt);
+					SQ.store_meta(s, sample, li);
+				}
 			}
 		}
 	}

@@ -36,6 +36,7 @@ struct rt_ctx {
 	// wavefront path
 	long long wave_width = 1 << 21;        // rays per round (RT_B200_WAVE overrides)
 	int walk_budget = 96;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
+	int n_area_lights = 0;                 // area + spot lights of the uploaded scene
 	bool budget_auto = true;               // no RT_B200_BUDGET given: the budget adapts to the scene
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
 	unsigned long long* pinned = nullptr;  // round counters read back by the host
@@ -150,7 +151,8 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 {
 	if (ctx->use_pool || A.prm.aterm_thresh > 0.0) return launch_pool(ctx, A); // adaptive termination needs the shadowed colour before it recurses
 	if (A.n_slots <= 0) return RT_OK;
-	const int L = ctx->S.n_lights;
+	// shadow rays one hit can make: one per point / directional light, softShadowRes per area or spot light
+	const int L = (ctx->S.n_lights - ctx->n_area_lights) + ctx->n_area_lights * (A.prm.soft_shadow_res > 0 ? A.prm.soft_shadow_res : 0);
 	long long W = ctx->wave_width;
 	const long long fit = ((A.n_slots + 1023) / 1024) * 1024;
 	if (W > fit) W = fit;
@@ -254,7 +256,7 @@ rt_status launch_pool(rt_ctx* ctx, PoolArgs& A)
 {
 	const int warps_per_block = RT_POOL_THREADS / 32;
 	const long long warps = (long long)ctx->pool_blocks * warps_per_block;
-	const bool defer = !(A.prm.aterm_thresh > 0.0);
+	const bool defer = !(A.prm.aterm_thresh > 0.0) && ctx->n_area_lights == 0; // the fused kernel defers one shadow ray per light only; area lights are shaded inline
 	A.cap = 32 * (A.depth + 3) + (defer ? 64 * ctx->S.n_lights + 64 : 0);
 	rt_status st;
 	if ((st = ensure(ctx, B_POOL_D, (size_t)warps * A.cap * RT_POOL_DOUBLES * sizeof(double))) != RT_OK) return st;
@@ -416,11 +418,11 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	CK(cudaSetDevice(ctx->device));
 	rt::ArenaView A(arena);
 	const rt_light* lights = A.ptr<rt_light>(RT_SEC_LIGHTS);
-	for (uint64_t k = 0; k < A.count(RT_SEC_LIGHTS); k++)
-		if (lights[k].type != RT_LIGHT_DIRECTIONAL && lights[k].type != RT_LIGHT_POINT) {
-			ctx->error = "area and spot lights are not implemented on the device path yet";
-			return RT_ERR_UNSUPPORTED;
-		}
+	int n_area = 0;
+	for (uint64_t k = 0; k < A.count(RT_SEC_LIGHTS); k++) {
+		if (lights[k].type < RT_LIGHT_DIRECTIONAL || lights[k].type > RT_LIGHT_SPOT) { ctx->error = "unknown light type"; return RT_ERR_ARG; }
+		if (lights[k].type >= RT_LIGHT_AREA_RECT) n_area++;
+	}
 	const long long n_snodes = (long long)A.count(RT_SEC_SCENE_NODES), n_mnodes = (long long)A.count(RT_SEC_MESH_NODES);
 	const long long n_mitems = (long long)A.count(RT_SEC_MESH_ITEMS), n_sitems = (long long)A.count(RT_SEC_SCENE_ITEMS);
 	const int n_mesh = (int)A.count(RT_SEC_MESHES);
@@ -494,6 +496,7 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	if (hflags[0]) { ctx->error = "invalid arena: index out of range (device check " + std::to_string(hflags[0]) + ")"; return RT_ERR_ARG; }
 	if ((hflags[1] | hflags[2]) & 0x80000000u || hflags[1] + hflags[2] > RT_STACK - 4) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
 	if (ctx->budget_auto) ctx->walk_budget = 96;
+	ctx->n_area_lights = n_area;
 	ctx->has_scene = true;
 	return RT_OK;
 }

@@ -11,7 +11,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-SCENES = ["hitchcock.ray", "trimesh2.ray", "dragon_small.ray", "mixed_small.ray", "prims_mixed.ray"]
+SCENES = ["hitchcock.ray", "trimesh2.ray", "dragon_small.ray", "mixed_small.ray", "prims_mixed.ray", "lights_area.ray"]
 W = 320
 TOL_WITHIN1 = 0.999
 

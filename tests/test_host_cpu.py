@@ -18,7 +18,7 @@ import numpy as np
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SMALL = ["hitchcock.ray", "trimesh2.ray", "prims_mixed.ray", "dragon_small.ray", "mixed_small.ray"]
+SMALL = ["hitchcock.ray", "trimesh2.ray", "prims_mixed.ray", "dragon_small.ray", "mixed_small.ray", "lights_area.ray"]
 
 
 # ---------------------------------------------------------------------------------------------
@@ -134,7 +134,7 @@ def test_device_code_on_host_hits_bit_exact(rtlib, oracle_mod, hostsim, scene_di
     assert np.abs(ref_rgb - rgb).max() < 1e-9
 
 
-@pytest.mark.parametrize("scene", ["hitchcock.ray", "prims_mixed.ray", "dragon_small.ray"])
+@pytest.mark.parametrize("scene", ["hitchcock.ray", "prims_mixed.ray", "dragon_small.ray", "lights_area.ray"])
 def test_device_code_on_host_frame_and_ray_counts(rtlib, oracle_mod, hostsim, scene_dir, scene):
     path = scene_dir / scene
     arena = rtlib.load_ray_file(str(path))

@@ -333,6 +333,7 @@ def run_b200(args, key, wl, rank, world, local_rank):
         # kernel walked (scenes/cost_model.json, per ray kind) / its device time
         cm = load_cost_model(key)
         peak, peak_src = measured_peaks()
+        fp64_peak, fp32_peak = ctx.measure_fma_peak()
         names = rt.Stats.STAGES
         out["stages"] = {names[k]: {"ms_per_step": stage_ms[k] / args.steps, "launches_per_step": stage_n[k] / args.steps} for k in range(6) if stage_n[k] > 0}
         if cm and stage_ms.sum() > 0:
@@ -349,7 +350,8 @@ def run_b200(args, key, wl, rank, world, local_rank):
                                "algorithmic_bytes_per_launch": alg_bytes / max(k_n, 1), "bytes_per_ray": ck["bytes_per_ray"],
                                "note": "the walk is FP64-latency bound, not bandwidth bound: the scene is L2 resident (DESIGN.md, roofline)",
                                "fp64": {"flops_per_ray": ck["flops_per_ray"], "achieved_tflops": ck["flops_per_ray"] * n_rays / (k_ms * 1e-3) / 1e12,
-                                        "peak_tflops": 37.0}}
+                                        "peak_tflops": fp64_peak,
+                                        "peak_source": "measured: rt_measure_fma_peak (8 FMA chains per thread)", "fp32_peak_tflops": fp32_peak}}
         else:
             out["roofline"] = None
         # the reference on this box's host cores, bounded sample (N = 1 only)

@@ -96,6 +96,8 @@ def lib():
     L.rt_selftest_division.restype = i32
     L.rt_selftest_derive.argtypes = [vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_ulonglong)]
     L.rt_selftest_derive.restype = i32
+    L.rt_measure_fma_peak.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+    L.rt_measure_fma_peak.restype = i32
     L.rt_set_profiling.argtypes = [vp, ctypes.c_int]
     L.rt_set_profiling.restype = i32
     L.rt_load_ray_file.argtypes = [cp, vp, ctypes.POINTER(vp), ctypes.POINTER(sz)]
@@ -212,6 +214,12 @@ class Context:
         bad = ctypes.c_ulonglong()
         self._check(lib().rt_selftest_derive(self._h, arena.ptr, arena.nbytes, ctypes.byref(bad)))
         return bad.value
+
+    def measure_fma_peak(self):
+        """(FP64, FP32) FMA TFLOP/s of this GPU."""
+        a, b = ctypes.c_double(), ctypes.c_double()
+        self._check(lib().rt_measure_fma_peak(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
 
     def set_profiling(self, on):
         """rt_set_profiling: per-stage CUDA-event times in Stats.stage_ms."""

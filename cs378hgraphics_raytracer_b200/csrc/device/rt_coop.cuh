@@ -19,7 +19,7 @@
 namespace rtd {
 
 #define RT_COOP_CAP 1536       // stack entries per warp (18 KB of shared memory)
-#define RT_COOP_WARPS 2        // warps per block of the heavy-ray kernel
+#define RT_COOP_WARPS 1        // warps per block of the heavy-ray kernel (47 KB of shared memory per warp)
 
 struct CoopStack {
 	int ref[RT_COOP_CAP];
@@ -125,86 +125,163 @@ __device__ __noinline__ void coop_mesh(const DTree& T, const DNode2* nodes, cons
 	best_pos = my_pos;
 }
 
-// Scene::intersect (scene.cpp:157-180) for one ray by one warp; all lanes hold the same ray and
-// return the same C.
-__device__ __forceinline__ void coop_closest(const DScene& S, const d3& ow, const d3& dw, TravClosest& C, CoopStack& K)
+// Scene-level shared state of one warp: its own stack (the mesh walk uses the other one) and the
+// list of trimesh candidates found so far, walked cooperatively one after the other (phase B).
+#define RT_COOP_SCENE_CAP 1024
+#define RT_COOP_MESH_LIST 128
+struct CoopScene {
+	int ref[RT_COOP_SCENE_CAP];
+	double ent[RT_COOP_SCENE_CAP];
+	int mesh_rank[RT_COOP_MESH_LIST];
+	double mesh_entry[RT_COOP_MESH_LIST];
+};
+
+// Phase B: the listed trimesh candidates, each by the whole warp.  C is warp-uniform.
+__device__ __noinline__ void coop_mesh_list(const DScene& S, const d3& ow, const d3& dw, const CoopScene& A, int n_list, TravClosest& C, CoopStack& K)
 {
-	int stk[RT_STACK];
-	double stke[RT_STACK];
+	for (int j = 0; j < n_list; j++) {
+		const double lim = C.have ? C.best_t : RT_T_INF;
+		if (A.mesh_entry[j] > lim) continue;
+		const int rank = A.mesh_rank[j];
+		const int obj = S.sitems[rank];
+		const rt_object& ob = S.objs[obj];
+		LocalRay L;
+		to_local(L, ob, ow, dw);
+		const DTree& T = S.mtrees[ob.mesh];
+		const int item_off = (int)S.meshes[ob.mesh].item_off;
+		RayInv Il;
+		RayF Fl;
+		make_inv(Il, Fl, L.o, L.d, S.mesh_slack[ob.mesh], S.mesh_slack[ob.mesh] * 1e9);
+		bool have;
+		double bt;
+		int bp;
+		coop_mesh(T, S.mnodes2 + T.node_off, S.mnodes2f + T.node_off, S.tris + item_off, L.o, L.d, Il, Fl, lim_to_local(lim, L.len), K, have, bt, bp);
+		if (have) {
+			const double t = bt / L.len;
+			if (!C.have || t < C.best_t || (t == C.best_t && rank < C.best_rank)) {
+				C.have = true;
+				C.best_t = t;
+				C.best_rank = rank;
+				C.best_obj = obj;
+				C.best_fpos = item_off + bp;
+			}
+		}
+	}
+}
+
+// Scene::intersect (scene.cpp:157-180) for one ray by one warp; all lanes hold the same ray and
+// return the same C.  Phase A walks the scene-level tree cooperatively (as coop_mesh does a mesh):
+// analytic candidates are tested by the lane that popped their leaf and kept as that lane's best;
+// trimesh candidates are only listed.  Phase B walks the listed meshes.  The final winner is
+// argmin (t, rank) over both groups - the reference's rule, independent of the visiting order.
+__device__ __forceinline__ void coop_closest(const DScene& S, const d3& ow, const d3& dw, TravClosest& C, CoopStack& K, CoopScene& A)
+{
+	const unsigned lane = threadIdx.x & 31;
+	const unsigned lt_mask = (1u << lane) - 1u;
+	const unsigned hi_mask = lane == 31 ? 0u : (0xffffffffu << (lane + 1));
 	RayInv I;
 	RayF F;
 	make_inv(I, F, ow, dw, S.scene_slack, S.scene_slack * 1e9);
-	double lim = RT_T_INF;
 	double e;
 	if (!box_hit(S.stree.lo, S.stree.hi, ow, dw, I, e)) return;
-	int sp = 0;
-	int cur = S.stree.root;
-	for (;;) {
-#pragma unroll 1
-		while (cur >= 0) {
-			const DNode2f& n = S.snodes2f[cur];
+	TravClosest mine; // this lane's best analytic candidate
+	mine.have = false;
+	mine.best_t = RT_T_INF;
+	mine.best_rank = 0x7fffffff;
+	mine.best_obj = -1;
+	mine.best_fpos = -1;
+	int n = 1, n_list = 0;
+	if (lane == 0) { A.ref[0] = S.stree.root; A.ent[0] = e; }
+	__syncwarp();
+	while (n > 0) {
+		const int take = n > RT_COOP_SCENE_CAP - 128 ? 1 : (n < 32 ? n : 32);
+		const bool has = (int)lane < take;
+		int ref = RT_REF_NONE;
+		double en = 0.0;
+		if (has) { ref = A.ref[n - 1 - lane]; en = A.ent[n - 1 - lane]; }
+		n -= take;
+		__syncwarp();
+		double lim = warp_min(mine.best_t);
+		if (C.have && C.best_t < lim) lim = C.best_t;
+		if (has && en > lim) ref = RT_REF_NONE;
+		int c0 = 0, c1 = 0, nc = 0;
+		double ce0 = 0.0, ce1 = 0.0;
+		if (ref != RT_REF_NONE && ref >= 0) {
+			const DNode2f& nd = S.snodes2f[ref];
 			double e0, e1;
 			bool h0, h1;
-			box2_hit(n, S.snodes2[cur], ow, dw, I, F, h0, h1, e0, e1);
+			box2_hit(nd, S.snodes2[ref], ow, dw, I, F, h0, h1, e0, e1);
 			h0 = h0 && !(e0 > lim);
 			h1 = h1 && !(e1 > lim);
-			const int c0 = n.c0, c1 = n.c1;
 			if (h0 && h1) {
 				const bool swap = e1 < e0;
-				stk[sp] = swap ? c0 : c1;
-				stke[sp] = swap ? e0 : e1;
-				sp++;
-				cur = swap ? c1 : c0;
-			} else if (h0) cur = c0;
-			else if (h1) cur = c1;
-			else cur = RT_REF_NONE;
+				c0 = swap ? nd.c0 : nd.c1; ce0 = swap ? e0 : e1;
+				c1 = swap ? nd.c1 : nd.c0; ce1 = swap ? e1 : e0;
+				nc = 2;
+			} else if (h0) { c0 = nd.c0; ce0 = e0; nc = 1; }
+			else if (h1) { c0 = nd.c1; ce0 = e1; nc = 1; }
 		}
-		if (cur != RT_REF_NONE) {
-			const int first = leaf_first(cur), count = leaf_count(cur);
+		// leaves: up to three candidates per lane; the loop is uniform so that meshes can be listed with a ballot
+		const bool leaf = ref != RT_REF_NONE && ref < 0;
+		const int first = leaf ? leaf_first(ref) : 0, count = leaf ? leaf_count(ref) : 0;
 #pragma unroll 1
-			for (int i = 0; i < count; i++) {
-				const int rank = first + i;
+		for (int i = 0; i < 3; i++) {
+			bool is_mesh = false;
+			double eb = 0.0;
+			const int rank = first + i;
+			if (i < count) {
 				const int obj = S.sitems[rank];
 				const rt_object& ob = S.objs[obj];
-				double eb;
-				if (!box_hit(ob.bbox, ob.bbox + 3, ow, dw, I, eb)) continue;
-				if (eb > lim) continue;
-				LocalRay L;
-				to_local(L, ob, ow, dw);
-				if (ob.type == RT_OBJ_TRIMESH) {
-					const DTree& T = S.mtrees[ob.mesh];
-					const int item_off = (int)S.meshes[ob.mesh].item_off;
-					RayInv Il;
-					RayF Fl;
-					make_inv(Il, Fl, L.o, L.d, S.mesh_slack[ob.mesh], S.mesh_slack[ob.mesh] * 1e9);
-					bool have;
-					double bt;
-					int bp;
-					coop_mesh(T, S.mnodes2 + T.node_off, S.mnodes2f + T.node_off, S.tris + item_off, L.o, L.d, Il, Fl, lim_to_local(lim, L.len), K, have, bt, bp);
-					if (have) {
-						const double t = bt / L.len;
-						if (!C.have || t < C.best_t || (t == C.best_t && rank < C.best_rank)) {
-							C.have = true;
-							C.best_t = t;
-							C.best_rank = rank;
-							C.best_obj = obj;
-							C.best_fpos = item_off + bp;
-						}
+				if (box_hit(ob.bbox, ob.bbox + 3, ow, dw, I, eb) && !(eb > lim)) {
+					if (ob.type == RT_OBJ_TRIMESH) is_mesh = true;
+					else {
+						LocalRay L;
+						to_local(L, ob, ow, dw);
+						prim_closest(ob, L, rank, obj, mine);
 					}
-				} else {
-					prim_closest(ob, L, rank, obj, C);
 				}
-				if (C.have) lim = C.best_t;
+			}
+			const unsigned mm = __ballot_sync(0xffffffffu, is_mesh);
+			if (mm) {
+				if (n_list + __popc(mm) > RT_COOP_MESH_LIST) { // list full: walk what is listed, then go on
+					__syncwarp();
+					coop_mesh_list(S, ow, dw, A, n_list, C, K);
+					n_list = 0;
+				}
+				if (is_mesh) { const int at = n_list + __popc(mm & lt_mask); A.mesh_rank[at] = rank; A.mesh_entry[at] = eb; }
+				n_list += __popc(mm);
+				__syncwarp();
 			}
 		}
-		for (;;) {
-			if (sp == 0) return;
-			sp--;
-			if (stke[sp] > lim) continue;
-			cur = stk[sp];
-			break;
+		const unsigned b1 = __ballot_sync(0xffffffffu, nc >= 1), b2 = __ballot_sync(0xffffffffu, nc == 2);
+		const int at = n + __popc(b1 & hi_mask) + __popc(b2 & hi_mask);
+		if (nc >= 1) { A.ref[at] = c0; A.ent[at] = ce0; }
+		if (nc == 2) { A.ref[at + 1] = c1; A.ent[at + 1] = ce1; }
+		n += __popc(b1) + __popc(b2);
+		__syncwarp();
+	}
+	// the lanes' analytic winners: argmin (t, rank)
+#pragma unroll
+	for (int o2 = 16; o2 > 0; o2 >>= 1) {
+		const double ot = __shfl_xor_sync(0xffffffffu, mine.best_t, o2);
+		const int orank = __shfl_xor_sync(0xffffffffu, mine.best_rank, o2);
+		const int oobj = __shfl_xor_sync(0xffffffffu, mine.best_obj, o2);
+		const bool oh = __shfl_xor_sync(0xffffffffu, mine.have ? 1 : 0, o2) != 0;
+		if (oh && (!mine.have || ot < mine.best_t || (ot == mine.best_t && orank < mine.best_rank))) {
+			mine.have = true;
+			mine.best_t = ot;
+			mine.best_rank = orank;
+			mine.best_obj = oobj;
 		}
 	}
+	if (mine.have && (!C.have || mine.best_t < C.best_t || (mine.best_t == C.best_t && mine.best_rank < C.best_rank))) {
+		C.have = true;
+		C.best_t = mine.best_t;
+		C.best_rank = mine.best_rank;
+		C.best_obj = mine.best_obj;
+		C.best_fpos = -1;
+	}
+	coop_mesh_list(S, ow, dw, A, n_list, C, K);
 }
 
 } // namespace rtd

@@ -259,6 +259,24 @@ __device__ __forceinline__ unsigned long long splitmix(unsigned long long& s)
 	z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
 	return z ^ (z >> 31);
 }
+// FMA throughput microbenchmark (MEASURED_PEAKS.json has no FP64 / FP32 SIMT peak):
+// 8 independent chains per thread, `iters` x 8 FMAs; the sum is written so nothing is optimised away.
+// Compiled in a TU built with -fmad=false, so the FMAs are spelled with the intrinsics.
+template <typename T> __device__ __forceinline__ T fma_t(T a, T b, T c);
+template <> __device__ __forceinline__ double fma_t<double>(double a, double b, double c) { return fma(a, b, c); }
+template <> __device__ __forceinline__ float fma_t<float>(float a, float b, float c) { return fmaf(a, b, c); }
+template <typename T> __global__ void __launch_bounds__(256) k_fma_peak(int iters, T seed, T* out)
+{
+	T a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+	const T m = (T)0.999, c = (T)0.001;
+#pragma unroll 4
+	for (int i = 0; i < iters; i++) {
+		a0 = fma_t<T>(a0, m, c); a1 = fma_t<T>(a1, m, c); a2 = fma_t<T>(a2, m, c); a3 = fma_t<T>(a3, m, c);
+		a4 = fma_t<T>(a4, m, c); a5 = fma_t<T>(a5, m, c); a6 = fma_t<T>(a6, m, c); a7 = fma_t<T>(a7, m, c);
+	}
+	out[(size_t)blockIdx.x * 256 + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+
 __global__ void __launch_bounds__(256) k_div_selftest(unsigned long long seed, long long n, int exp_range, unsigned long long* mismatches)
 {
 	const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;

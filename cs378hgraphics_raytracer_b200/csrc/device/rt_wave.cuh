@@ -154,7 +154,9 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_clos
 __global__ void __launch_bounds__(32 * RT_COOP_WARPS) k_wave_closest_heavy(const __grid_constant__ DScene S, const RayQueue Q, long long base, const HitQueue H, const int* heavy, WaveCounters* cnt)
 {
 	__shared__ CoopStack stacks[RT_COOP_WARPS];
+	__shared__ CoopScene scenes[RT_COOP_WARPS];
 	CoopStack& K = stacks[threadIdx.x >> 5];
+	CoopScene& A = scenes[threadIdx.x >> 5];
 	const unsigned lane = threadIdx.x & 31;
 	const unsigned long long n = cnt->n_heavy;
 	for (;;) {
@@ -171,7 +173,7 @@ __global__ void __launch_bounds__(32 * RT_COOP_WARPS) k_wave_closest_heavy(const
 		C.best_rank = 0x7fffffff;
 		C.best_obj = -1;
 		C.best_fpos = -1;
-		coop_closest(S, ro, rd, C, K);
+		coop_closest(S, ro, rd, C, K, A);
 		if (lane == 0) {
 			H.t[k] = C.have ? C.best_t : -1.0;
 			H.of[k] = make_int2(C.best_obj, C.best_fpos);

@@ -218,7 +218,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt));
 		if (ctx->walk_budget > 0)
-			STAGE(RT_STAGE_COOP, k_wave_closest_heavy<<<ctx->sm_count * 4, 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt));
+			STAGE(RT_STAGE_COOP, k_wave_closest_heavy<<<ctx->sm_count * 4 * (2 / RT_COOP_WARPS), 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt));
 		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
 		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
@@ -790,6 +790,32 @@ rt_status rt_selftest_division(rt_ctx* ctx, long long n, unsigned long long seed
 	CK(cudaGetLastError());
 	CK(cudaMemcpyAsync(mismatches, cnt, 8, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream));
+	return RT_OK;
+}
+
+
+rt_status rt_measure_fma_peak(rt_ctx* ctx, double* fp64_tflops, double* fp32_tflops)
+{
+	if (!ctx || !fp64_tflops || !fp32_tflops) return RT_ERR_ARG;
+	CK(cudaSetDevice(ctx->device));
+	const int blocks = ctx->sm_count * 8, iters = 1 << 14;
+	rt_status st;
+	if ((st = ensure(ctx, B_TMP_A, (size_t)blocks * 256 * sizeof(double))) != RT_OK) return st;
+	double best[2] = {0.0, 0.0};
+	for (int rep = 0; rep < 4; rep++)
+		for (int k = 0; k < 2; k++) {
+			CK(cudaEventRecord(ctx->ev0, ctx->stream));
+			if (k == 0) k_fma_peak<double><<<blocks, 256, 0, ctx->stream>>>(iters, 1.0, (double*)ctx->buf[B_TMP_A]);
+			else k_fma_peak<float><<<blocks, 256, 0, ctx->stream>>>(iters, 1.0f, (float*)ctx->buf[B_TMP_A]);
+			CK(cudaEventRecord(ctx->ev1, ctx->stream));
+			CK(cudaEventSynchronize(ctx->ev1));
+			float ms = 0.f;
+			CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+			const double tf = 2.0 * 8.0 * iters * (double)blocks * 256 / (ms * 1e-3) / 1e12;
+			if (rep > 0 && tf > best[k]) best[k] = tf; // first pass warms up
+		}
+	*fp64_tflops = best[0];
+	*fp32_tflops = best[1];
 	return RT_OK;
 }
 

@@ -141,6 +141,10 @@ rt_status rt_selftest_division(rt_ctx* ctx, long long n, unsigned long long seed
  * (the arena of the last upload) are compared byte for byte with the host construction. */
 rt_status rt_selftest_derive(rt_ctx* ctx, const void* arena, size_t bytes, unsigned long long* mismatches);
 
+/* FP64 and FP32 FMA throughput of this GPU (TFLOP/s, FMA = 2), measured with a dependent-chain
+ * microbenchmark: the compute ceilings bench.py's roofline quotes next to the HBM one. */
+rt_status rt_measure_fma_peak(rt_ctx* ctx, double* fp64_tflops, double* fp32_tflops);
+
 /* ---- host-side scene loading (no GPU needed) -------------------------------------------- */
 /* Replaces Tokenizer + Parser::parseScene + Scene::add/conclude + Trimesh::conclude (reference
  * parser/Parser.cpp:26-95, scene.cpp:133-153, trimesh.cpp:69-77, kdTree.h:23-78): parses a .ray

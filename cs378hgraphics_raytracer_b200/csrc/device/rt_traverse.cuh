@@ -193,8 +193,6 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 	RayInv I;
 	RayF F;
 	make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
-	const RayInv Iw = I; // world-space copies, restored when the walk leaves a mesh
-	const RayF Fw = F;
 	const DNode2* nodes = S.snodes2;
 	const DNode2f* nodesf = S.snodes2f;
 	const DTri* tris = S.tris;
@@ -219,11 +217,11 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 			const DNode2f& nf = nodesf[cur];
 			RT_CNT(nodes, mode);
 			if (budget > 0 && --budget == 0) return false;
+			const int c0 = nf.c0, c1 = nf.c1;
 			double e0, e1;
 			bool h0, h1;
 			box2_hit(nf, nodes[cur], o, d, I, F, h0, h1, e0, e1);
 			if (prune) { h0 = h0 && !(e0 > lim); h1 = h1 && !(e1 > lim); }
-			const int c0 = nf.c0, c1 = nf.c1;
 			if (h0 && h1) {
 				const bool swap = prune && e1 < e0;
 				stk[sp] = swap ? c0 : c1;
@@ -329,8 +327,7 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 					}
 					o = ow;
 					d = dw;
-					I = Iw;
-					F = Fw;
+					make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9); // recomputed: keeping a copy costs more in spills
 					nodes = S.snodes2;
 					nodesf = S.snodes2f;
 					level = 0;

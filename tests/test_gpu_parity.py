@@ -290,3 +290,30 @@ def test_cli_renders_reference_frame(rtlib, oracle_mod, scene_dir, tmp_path):
     ref_img, _, _ = orc.render(rtlib.Params.default(depth=5), w, h)
     d = oracle_mod.image_diff(ref_img, px)
     assert d["within1"] >= TOL_WITHIN1, d
+
+
+GOLDEN = {"hitchcock": "hitchcock.ray", "trimesh2": "trimesh2.ray", "dragon_small": "dragon_small.ray", "prims_mixed": "prims_mixed.ray",
+          "lights_area": "lights_area.ray"}
+
+
+@pytest.mark.parametrize("name", sorted(GOLDEN))
+def test_golden_vectors(rtlib, ctx, scene_dir, name):
+    """Committed outputs of the unmodified reference (tests/golden/make_golden.py): hit records of
+    every camera ray bit-exact, traceRay colours, the RGB8 frame and the ray counters.  Needs no
+    oracle library on the box."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    arena = rtlib.load_ray_file(str(scene_dir / GOLDEN[name]))
+    ctx.upload(arena)
+    w, h, depth = int(g["w"]), int(g["h"]), int(g["depth"])
+    p = rtlib.Params.default(depth=depth)
+    hits, rgb = ctx.trace_rays(p, g["rays"], depth)
+    assert np.array_equal(hits["obj"], g["obj"])
+    assert np.array_equal(hits["face"], g["face"])
+    assert np.array_equal(hits["t"], g["t"])
+    assert np.array_equal(hits["N"], g["N"])
+    assert np.abs(rgb - g["rgb"]).max() < 1e-9
+    img, st = ctx.render(p, w, h)
+    d = np.abs(img.astype(np.int32) - g["frame"].astype(np.int32)).max(axis=2)
+    assert (d <= 1).mean() >= TOL_WITHIN1
+    assert [st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays] == [int(x) for x in g["counts"]]

@@ -164,3 +164,32 @@ def test_cli_fails_loudly_without_gpu(scene_dir, tmp_path):
     assert r.returncode == 1
     assert "no CUDA device" in r.stderr
     assert not (tmp_path / "o.bmp").exists()
+
+
+GOLDEN = {"hitchcock": "hitchcock.ray", "trimesh2": "trimesh2.ray", "dragon_small": "dragon_small.ray", "prims_mixed": "prims_mixed.ray",
+          "lights_area": "lights_area.ray"}
+
+
+@pytest.mark.parametrize("name", sorted(GOLDEN))
+def test_golden_vectors_hostsim(rtlib, hostsim, scene_dir, name):
+    """The committed reference outputs (tests/golden) against the host build of the device code:
+    runs without the oracle library."""
+    from cs378hgraphics_raytracer_b200.binding import HIT_DTYPE
+    g = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    arena = rtlib.load_ray_file(str(scene_dir / GOLDEN[name]))
+    w, h, depth = int(g["w"]), int(g["h"]), int(g["depth"])
+    p = rtlib.Params.default(depth=depth)
+    rays = np.ascontiguousarray(g["rays"])
+    n = len(rays)
+    hits = np.zeros(n, HIT_DTYPE)
+    rgb = np.zeros((n, 3))
+    assert hostsim.sim_trace_rays(arena.ptr, ctypes.byref(p), rays.ctypes.data, n, depth, hits.ctypes.data, rgb.ctypes.data, 1) == 0
+    for f in ("obj", "face", "t", "N"):
+        assert np.array_equal(hits[f], g[f]), f
+    assert np.abs(rgb - g["rgb"]).max() < 1e-9
+    img = np.zeros((h, w, 3), np.uint8)
+    st = rtlib.Stats()
+    assert hostsim.sim_render(arena.ptr, ctypes.byref(p), w, h, img.ctypes.data, ctypes.byref(st)) == 0
+    d = np.abs(img.astype(np.int32) - g["frame"].astype(np.int32)).max(axis=2)
+    assert (d <= 1).mean() >= 0.999
+    assert [st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays] == [int(x) for x in g["counts"]]

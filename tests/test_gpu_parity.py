@@ -317,3 +317,29 @@ def test_golden_vectors(rtlib, ctx, scene_dir, name):
     d = np.abs(img.astype(np.int32) - g["frame"].astype(np.int32)).max(axis=2)
     assert (d <= 1).mean() >= TOL_WITHIN1
     assert [st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays] == [int(x) for x in g["counts"]]
+
+
+@pytest.mark.parametrize("scene", ["prims_mixed.ray", "hitchcock.ray"])
+def test_small_wave_width_spills(rtlib, oracle_mod, scene_dir, scene, monkeypatch):
+    """With only 1024 rays per round the children of a round exceed the round width on glass and
+    mirror surfaces: the excess goes through the spill stack (rt_api.cu: launch_wave).  Same frame,
+    same ray counts, many more rounds."""
+    monkeypatch.setenv("RT_B200_WAVE", "1024")
+    c = rtlib.Context(0)
+    try:
+        path = scene_dir / scene
+        arena = rtlib.load_ray_file(str(path))
+        c.upload(arena)
+        orc = oracle_mod.Oracle(str(path))
+        w = 160
+        h = oracle_mod.frame_height(w, orc.aspect)
+        p = rtlib.Params.default(depth=6)
+        ref_img, ref_st, _ = orc.render(p, w, h)
+        img, st = c.render(p, w, h)
+        assert st.rounds > 20
+        d = oracle_mod.image_diff(ref_img, img)
+        assert d["within1"] >= TOL_WITHIN1, d
+        assert (st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays) == \
+            (ref_st.camera_rays, ref_st.reflection_rays, ref_st.refraction_rays, ref_st.shadow_rays)
+    finally:
+        c.close()

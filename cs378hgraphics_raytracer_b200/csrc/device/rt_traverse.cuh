@@ -327,7 +327,9 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 					}
 					o = ow;
 					d = dw;
-					make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9); // recomputed: keeping a copy costs more in spills
+					// world-space inverse again (recomputed: keeping a copy costs more in spills), unless
+					// nothing is left to test with it
+					if (sp > 0) make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
 					nodes = S.snodes2;
 					nodesf = S.snodes2f;
 					level = 0;

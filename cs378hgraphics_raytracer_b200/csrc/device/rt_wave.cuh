@@ -184,7 +184,10 @@ __global__ void __launch_bounds__(32 * RT_COOP_WARPS) k_wave_closest_heavy(const
 }
 
 // ---- stage 2: RayTracer::traceRay's body --------------------------------------------------------
-__global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_shade(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue Q, long long base, long long m, const HitQueue H,
+#ifndef RT_SHADE_MINB
+#define RT_SHADE_MINB 4
+#endif
+__global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue Q, long long base, long long m, const HitQueue H,
                                                                  const RayQueue Nxt, const RayQueue SQ, int parity, WaveCounters* cnt)
 {
 	const unsigned lane = threadIdx.x & 31;

@@ -91,8 +91,14 @@ RT_HD d3 mul33(const double* m, d3 v)
 struct RayInv {
 	d3 y;          // 1/d per axis (IEEE)
 	double slmax;  // pruning slack: max over the axes with d != 0 of slack/|d|
-	unsigned span; // width of the exponent window of `a` served by the FMA path: 1201, or 0 when
-	               // some |d| lies outside [2^-300, 2^300] (every quotient is then a real division)
+	float guard;   // one register for two rarely-used facts:
+	               //   NaN  - some |d| lies outside [2^-300, 2^300]: every quotient is a real division
+	               //   >= 0 - pruned walk of a ray with a zero direction component: boxes farther than
+	               //          this from the origin along that axis are refused (rt_prims.cuh)
+	               //   < 0  - neither
+	RT_HD bool fma_ok() const { return guard == guard; }
+	// width of the exponent window of `a` served by div_by's FMA path
+	RT_HD unsigned span() const { return fma_ok() ? 1201u : 0u; }
 };
 // Single-precision image of the ray for the box PRE-test (rt_prims.cuh: box2_hit).  With node boxes
 // rounded to float, every slab quotient computed in float differs from the reference's double
@@ -131,7 +137,9 @@ RT_HD void make_inv(RayInv& I, const d3& d, double slack)
 	if (d.x != 0.0) I.slmax = sl.x;
 	if (d.y != 0.0 && sl.y > I.slmax) I.slmax = sl.y;
 	if (d.z != 0.0 && sl.z > I.slmax) I.slmax = sl.z;
-	I.span = (div_range_ok(d.x) && div_range_ok(d.y) && div_range_ok(d.z)) ? 1201u : 0u;
+	const bool zero = d.x == 0.0 || d.y == 0.0 || d.z == 0.0;
+	I.guard = zero && slack > 0.0 && slack < 1e30 ? (float)slack * 1.0001f + 1e-37f : -1.0f;
+	if (!(div_range_ok(d.x) && div_range_ok(d.y) && div_range_ok(d.z))) I.guard = NAN; // no FMA path, no refusal either
 }
 RT_HD unsigned biased_exp(double a)
 {

@@ -13,13 +13,23 @@ namespace rtd {
 //
 // box_hit_exact: the six quotients are correctly rounded (div_by, rt_math.cuh), i.e. the
 // reference's own numbers.
+//
+// Zero direction components.  The reference skips an axis with d == 0 altogether (bbox.cc:43), so
+// a ray of the centre pixel column (d.x == 0) "touches" every box whose other two slabs it crosses,
+// wherever the box lies along x: tens of thousands of nodes per ray, all of whose items then fail
+// their own intersection test.  A PRUNED walk (I.guard >= 0: set for rays that have a zero component) may refuse such a box when the origin
+// lies outside its slab by more than the guard distance (1e-9 of the tree's extent): every item
+// under the box lies inside it, the ray never comes closer to it than the guard along that axis,
+// and a hit needs the intersection point inside the item up to rounding (1e-16 relative), so the
+// refused subtree holds no candidate the reference would have accepted - the same argument as for
+// distance pruning: the box test only filters candidates, the winner is chosen among the items.
 RT_COLD bool box_hit_exact(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
 {
 	double tMin = -1.0e308, tMax = 1.0e308;
 #define RT_SLAB(O, D, Y, LO, HI)                                            \
 	if (D != 0.0) {                                                         \
-		double t1 = div_by(LO - O, D, Y, I.span);                           \
-		double t2 = div_by(HI - O, D, Y, I.span);                           \
+		double t1 = div_by(LO - O, D, Y, I.span());                           \
+		double t2 = div_by(HI - O, D, Y, I.span());                           \
 		if (t1 > t2) { double tt = t1; t1 = t2; t2 = tt; }                  \
 		if (t1 > tMin) tMin = t1;                                           \
 		if (t2 < tMax) tMax = t2;                                           \
@@ -44,9 +54,18 @@ RT_COLD bool box_hit_exact(const double* bmin, const double* bmax, const d3& o, 
 //     tMax~ - tMin~ > s, tMax~ > EPS+1e-20 =>  neither                 : hit
 // and only the sliver in between (grazing rays, boxes touching the origin) takes box_hit_exact.
 // Non-finite or denormal intermediates fail all three tests and fall through to it as well.
+// the zero-component refusal described above; only rays that have such a component get here
+RT_COLD bool zero_axis_outside(const double* bmin, const double* bmax, const d3& o, const d3& d, double g)
+{
+	if (d.x == 0.0 && (o.x < bmin[0] - g || o.x > bmax[0] + g)) return true;
+	if (d.y == 0.0 && (o.y < bmin[1] - g || o.y > bmax[1] + g)) return true;
+	if (d.z == 0.0 && (o.z < bmin[2] - g || o.z > bmax[2] + g)) return true;
+	return false;
+}
+
 RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
 {
-	if (I.span != 0u) {
+	if (I.fma_ok()) {
 		double tn = -1.0e308, tf = 1.0e308;
 #define RT_SLAB(O, D, Y, LO, HI)                                            \
 		if (D != 0.0) {                                                     \
@@ -68,6 +87,19 @@ RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3
 	return box_hit_exact(bmin, bmax, o, d, I, entry);
 }
 
+// Tree nodes (never the per-object bounding boxes, whose pre-test stays the reference's): box_hit
+// plus the zero-component refusal.  Such rays have F.amax = +inf, so all their node tests come here.
+#ifndef RT_NODE_ATTR
+#define RT_NODE_ATTR RT_HD
+#endif
+RT_NODE_ATTR bool box_hit_node(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
+{
+#ifndef RT_NO_ZERO_GUARD
+	if (I.guard >= 0.0f && zero_axis_outside(bmin, bmax, o, d, (double)I.guard)) { entry = 0.0; return false; }
+#endif
+	return box_hit(bmin, bmax, o, d, I, entry);
+}
+
 // Both children of a node at once, float first.  Per child the float test ends in one of three
 // states: certainly hit, certainly missed (by the margins derived at RayF), or ambiguous - and only
 // an ambiguous child reads its double box and takes box_hit.  e0/e1 are conservative entry
@@ -85,7 +117,7 @@ RT_HD void box2_hit(const DNode2f& nf, const DNode2& n, const d3& o, const d3& d
 		const float gap = tf - tn;                                                               \
 		if (gap < -s || tf + s < (float)RT_RAY_EPSILON) { H = false; E = 0.0; }                  \
 		else if (gap > s && tf - s > (float)RT_RAY_EPSILON * 1.0001f) { H = true; E = (double)(tn - s) - I.slmax; } \
-		else H = box_hit(LO64, HI64, o, d, I, E);                                                \
+		else H = box_hit_node(LO64, HI64, o, d, I, E);                                           \
 	}
 	RT_BOXF(nf.lo0, nf.hi0, h0, e0, n.lo0, n.hi0)
 	RT_BOXF(nf.lo1, nf.hi1, h1, e1, n.lo1, n.hi1)

@@ -35,6 +35,7 @@ struct TravWork {
 };
 inline thread_local TravWork g_work;
 inline unsigned long long g_work_dump = ~0ull; // print rays whose walk visits more nodes than this
+inline thread_local unsigned* g_walk_log = nullptr; // when set: (mode, nodes) of every walk, g_walk_log[0] = entries used, g_walk_log[1] = capacity
 struct WorkScope {
 	int mode;
 	unsigned long long n0, t0;
@@ -43,6 +44,7 @@ struct WorkScope {
 	~WorkScope()
 	{
 		const unsigned long long n = g_work.nodes[mode] - n0;
+		if (g_walk_log && g_walk_log[0] < g_walk_log[1]) { g_walk_log[2 + 2 * g_walk_log[0]] = (unsigned)mode; g_walk_log[3 + 2 * g_walk_log[0]] = (unsigned)n; g_walk_log[0]++; }
 		if (n > g_work_dump) fprintf(stderr, "walk mode %d nodes %llu tris %llu o %.17g %.17g %.17g d %.17g %.17g %.17g\n", mode, n, g_work.tris[mode] - t0, o.x, o.y, o.z, d.x, d.y, d.z);
 		int b = 0;
 		while ((n + 1) >> (b + 1)) b++;

@@ -206,4 +206,37 @@ int sim_work(const void* arena, const rt_params* prm, int w, int h, unsigned lon
 	return 0;
 }
 
+// Per-pixel walk lengths of a depth-0 frame (lane-utilisation analysis, profiles/simt_model.py):
+// out[pixel * slots + 0] = nodes of the camera ray's walk, out[pixel * slots + 1 + k] = nodes of its
+// k-th shadow walk (k < slots - 1; later ones are added to the last slot)
+int sim_walk_lengths(const void* arena, const rt_params* prm, int w, int h, int slots, unsigned* out)
+{
+	Sim sim;
+	setup(sim, arena);
+	rt_params p = *prm;
+	p.depth = 0;
+	std::memset(out, 0, sizeof(unsigned) * (size_t)w * h * slots);
+#pragma omp parallel
+	{
+		std::vector<unsigned> log(2 + 2 * 4096);
+#pragma omp for collapse(2) schedule(dynamic, 16)
+		for (int j = 0; j < h; j++)
+			for (int i = 0; i < w; i++) {
+				log[0] = 0;
+				log[1] = 4096;
+				g_walk_log = log.data();
+				const double x = double(i) / double(w), y = double(j) / double(h);
+				sample_colour<true>(sim.S, p, x, y, nullptr);
+				g_walk_log = nullptr;
+				unsigned* o = out + ((size_t)j * w + i) * slots;
+				int ks = 0;
+				for (unsigned e = 0; e < log[0]; e++) {
+					if (log[2 + 2 * e] == 0) o[0] += log[3 + 2 * e];
+					else { o[1 + (ks < slots - 2 ? ks : slots - 2)] += log[3 + 2 * e]; ks++; }
+				}
+			}
+	}
+	return 0;
+}
+
 } // extern "C"

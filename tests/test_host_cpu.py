@@ -152,6 +152,32 @@ def test_device_code_on_host_frame_and_ray_counts(rtlib, oracle_mod, hostsim, sc
         (ref_st.camera_rays, ref_st.reflection_rays, ref_st.refraction_rays, ref_st.shadow_rays)
 
 
+@pytest.mark.parametrize("scene", ["dragon_small.ray", "mixed_small.ray", "prims_mixed.ray", "lights_area.ray"])
+def test_zero_direction_component_rays(rtlib, oracle_mod, hostsim, scene_dir, scene):
+    """Rays with an exactly zero direction component (centre pixel column / row): the reference's slab
+    test skips that axis (bbox.cc:43); the pruned walk refuses boxes the origin lies outside of along
+    it (rt_prims.cuh) - the winner, t and the colour of the whole ray tree must not move."""
+    from cs378hgraphics_raytracer_b200.binding import HIT_DTYPE
+    path = scene_dir / scene
+    arena = rtlib.load_ray_file(str(path))
+    orc = oracle_mod.Oracle(str(path))
+    w = 640
+    h = oracle_mod.frame_height(w, orc.aspect)
+    rays = oracle_mod.camera_rays(arena.camera(), w, h).reshape(h, w, 6)
+    rays = np.ascontiguousarray(np.concatenate([rays[:, w // 2], rays[h // 2, :]]))
+    assert (rays[:, 3:6] == 0).any(axis=1).sum() >= h
+    n = len(rays)
+    p = rtlib.Params.default(depth=4)
+    ref_hits, ref_rgb = orc.trace_rays(p, rays, 4)
+    hits = np.zeros(n, HIT_DTYPE)
+    rgb = np.zeros((n, 3))
+    assert hostsim.sim_trace_rays(arena.ptr, ctypes.byref(p), rays.ctypes.data, n, 4, hits.ctypes.data, rgb.ctypes.data, 1) == 0
+    assert (ref_hits["obj"] >= 0).sum() > 20
+    for f in ("obj", "face", "t", "N"):
+        assert np.array_equal(ref_hits[f], hits[f]), f
+    assert np.abs(ref_rgb - rgb).max() < 1e-9
+
+
 def test_cli_fails_loudly_without_gpu(scene_dir, tmp_path):
     """ray_b200 (C++ RayTracer mirror + the reference's command line) has no CPU path either."""
     import torch

@@ -229,8 +229,8 @@ __device__ __forceinline__ void coop_closest(const DScene& S, const d3& ow, cons
 			bool is_mesh = false;
 			double eb = 0.0;
 			const int rank = first + i;
-			if (i < count) {
-				const int obj = S.sitems[rank];
+			if (i < count && !box_miss_f(S.sboxf[rank], F)) {
+				const int obj = S.sboxf[rank].obj;
 				const rt_object& ob = S.objs[obj];
 				if (box_hit(ob.bbox, ob.bbox + 3, ow, dw, I, eb) && !(eb > lim)) {
 					if (ob.type == RT_OBJ_TRIMESH) is_mesh = true;

@@ -12,6 +12,7 @@ namespace rtd {
 struct Derived {
 	std::vector<DNode2> snodes2, mnodes2;
 	std::vector<DNode2f> snodes2f, mnodes2f;
+	std::vector<DItemBox> sboxf;
 	DTree stree;
 	std::vector<DTree> mtrees;
 	std::vector<DTri> tris;
@@ -119,6 +120,17 @@ inline void derive(const rt::ArenaView& A, Derived& D)
 	D.max_scene_depth = tree_depth(snodes, A.count(RT_SEC_SCENE_NODES));
 	nodes_to_float(D.snodes2, D.snodes2f);
 	nodes_to_float(D.mnodes2, D.mnodes2f);
+	const int32_t* sitems = A.ptr<int32_t>(RT_SEC_SCENE_ITEMS);
+	const rt_object* objs = A.ptr<rt_object>(RT_SEC_OBJECTS);
+	D.sboxf.resize(A.count(RT_SEC_SCENE_ITEMS));
+	for (size_t k = 0; k < D.sboxf.size(); k++) {
+		DItemBox& b = D.sboxf[k];
+		std::memset(&b, 0, sizeof(b));
+		const int32_t obj = sitems[k];
+		if (obj < 0 || (uint64_t)obj >= A.count(RT_SEC_OBJECTS)) continue;
+		for (int c = 0; c < 3; c++) { b.lo[c] = (float)objs[obj].bbox[c]; b.hi[c] = (float)objs[obj].bbox[3 + c]; }
+		b.obj = obj;
+	}
 }
 
 } // namespace rtd

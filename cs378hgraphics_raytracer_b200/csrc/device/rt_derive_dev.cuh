@@ -78,6 +78,25 @@ __global__ void __launch_bounds__(256) k_derive_nodes2f(const DNode2* in, long l
 	out[k] = f;
 }
 
+// float image of the candidates' world boxes, in leaf item order (bad item indices are reported by
+// k_derive_check; their slot is left zeroed)
+__global__ void __launch_bounds__(256) k_derive_itembox(const int32_t* sitems, long long n_sitems, const rt_object* objs, long long n_obj, DItemBox* out)
+{
+	const long long k = (long long)blockIdx.x * 256 + threadIdx.x;
+	if (k >= n_sitems) return;
+	DItemBox b;
+	const int32_t obj = sitems[k];
+	const bool ok = obj >= 0 && obj < n_obj;
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		b.lo[c] = ok ? (float)objs[obj].bbox[c] : 0.0f;
+		b.hi[c] = ok ? (float)objs[obj].bbox[3 + c] : 0.0f;
+	}
+	b.obj = ok ? obj : 0;
+	b.pad = 0;
+	out[k] = b;
+}
+
 __device__ __forceinline__ double dev_box_extent(const rt_node& n)
 {
 	double m = 1.0;

@@ -90,7 +90,7 @@ RT_HD bool box_hit(const double* bmin, const double* bmax, const d3& o, const d3
 // Tree nodes (never the per-object bounding boxes, whose pre-test stays the reference's): box_hit
 // plus the zero-component refusal.  Such rays have F.amax = +inf, so all their node tests come here.
 #ifndef RT_NODE_ATTR
-#define RT_NODE_ATTR RT_HD
+#define RT_NODE_ATTR RT_COLD // out of line: the hot loop keeps only the float test (profiles/r1_variants.txt)
 #endif
 RT_NODE_ATTR bool box_hit_node(const double* bmin, const double* bmax, const d3& o, const d3& d, const RayInv& I, double& entry)
 {
@@ -122,6 +122,21 @@ RT_HD void box2_hit(const DNode2f& nf, const DNode2& n, const d3& o, const d3& d
 	RT_BOXF(nf.lo0, nf.hi0, h0, e0, n.lo0, n.hi0)
 	RT_BOXF(nf.lo1, nf.hi1, h1, e1, n.lo1, n.hi1)
 #undef RT_BOXF
+}
+
+// Object bounding boxes (Geometry::intersect's pre-test, scene.cpp:15): true when the float test
+// proves that the reference's double test answers "miss" (same margins as box2_hit); anything
+// else - hit, ambiguous, zero direction components (amax = inf), NaN - is false and the caller runs
+// the double test on the object's own box.
+RT_HD bool box_miss_f(const DItemBox& b, const RayF& F)
+{
+	const float qx1 = (b.lo[0] - F.ox) * F.yx, qx2 = (b.hi[0] - F.ox) * F.yx;
+	const float qy1 = (b.lo[1] - F.oy) * F.yy, qy2 = (b.hi[1] - F.oy) * F.yy;
+	const float qz1 = (b.lo[2] - F.oz) * F.yz, qz2 = (b.hi[2] - F.oz) * F.yz;
+	const float tn = fmaxf(fmaxf(fminf(qx1, qx2), fminf(qy1, qy2)), fminf(qz1, qz2));
+	const float tf = fminf(fminf(fmaxf(qx1, qx2), fmaxf(qy1, qy2)), fmaxf(qz1, qz2));
+	const float s = 2.0f * F.amax + 0x1p-20f * (fabsf(tn) + fabsf(tf));
+	return tf - tn < -s || tf + s < (float)RT_RAY_EPSILON;
 }
 
 // What a primitive's intersectLocal leaves in the isect (object space).

@@ -36,6 +36,14 @@ struct alignas(64) DNode2f {
 	int32_t c0, c1;
 	int32_t pad[2];
 };
+// One scene-level leaf item (position = candidate rank): the object's world bounding box rounded to
+// float plus its index, so that a candidate the ray certainly misses costs one 32-byte read and a
+// float slab test instead of the rt_object record and the double test (rt_prims.cuh: box_miss_f).
+struct alignas(32) DItemBox {
+	float lo[3], hi[3];
+	int32_t obj;
+	int32_t pad;
+};
 #define RT_REF_MESH_EXIT ((int32_t)0x80000000)
 #define RT_REF_NONE ((int32_t)0x80000001)
 RT_HD int32_t leaf_ref(int32_t first, int32_t count) { return -(1 + ((first << 2) | count)); }
@@ -55,6 +63,7 @@ struct DScene {
 	const DNode2* mnodes2;
 	const DNode2f* snodes2f; // float images, same indexing
 	const DNode2f* mnodes2f;
+	const DItemBox* sboxf;   // per scene leaf item
 	const DTree* mtrees; // per mesh
 	const rt_node* snodes;
 	const int32_t* sitems;

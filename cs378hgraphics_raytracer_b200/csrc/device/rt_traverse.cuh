@@ -262,9 +262,11 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 #pragma unroll 1
 				for (int i = 0; i < count; i++) {
 					const int rank = first + i;
-					const int obj = S.sitems[rank];
-					const rt_object& ob = S.objs[obj];
+					const DItemBox& ib = S.sboxf[rank];
 					RT_CNT(objs, mode);
+					if (box_miss_f(ib, F)) continue;
+					const int obj = ib.obj;
+					const rt_object& ob = S.objs[obj];
 					// Geometry::intersect / intersectList: world-bbox pretest (scene.cpp:15,43) is a real
 					// filter (leaf boxes are unions), then the object-space test
 					double eb;

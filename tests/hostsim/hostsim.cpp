@@ -29,6 +29,7 @@ void setup(Sim& sim, const void* arena)
 	S.mnodes2 = sim.D.mnodes2.data();
 	S.snodes2f = sim.D.snodes2f.data();
 	S.mnodes2f = sim.D.mnodes2f.data();
+	S.sboxf = sim.D.sboxf.data();
 	S.mtrees = sim.D.mtrees.data();
 	S.snodes = A.ptr<rt_node>(RT_SEC_SCENE_NODES);
 	S.sitems = A.ptr<int32_t>(RT_SEC_SCENE_ITEMS);

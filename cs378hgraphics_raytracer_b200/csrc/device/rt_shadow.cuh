@@ -36,6 +36,8 @@ struct SBuf {
 	double floor_t;     // only hits with (t,key) > (floor_t,floor_key) are collected
 	unsigned long long floor_key;
 	double min_dropped; // smallest t that was dropped for lack of space
+	double sure_t;      // an entered opaque surface at t <= sure_t makes the result exactly 0 (see sbuf_add)
+	bool dead;          // such a surface was found: the walk can stop, srsAttenuation returns dvec3(0)
 };
 
 RT_HD bool key_less(double ta, unsigned long long ka, double tb, unsigned long long kb) { return ta < tb || (ta == tb && ka < kb); }
@@ -48,6 +50,14 @@ RT_COLD void sbuf_add(SBuf& B, double t, unsigned long long key, bool inside, bo
 	// 0; leaving a medium with kt = 0 zeroes the attenuation (unless delta is exactly 0, which the
 	// walk detects and answers with another pass)
 	const bool term = inside ? (kt.x == 0.0 && kt.y == 0.0 && kt.z == 0.0) : !trans;
+	// Any-hit exit.  srsAttenuation's loop can only return something other than 0 before it reaches
+	// an entered opaque surface through the light's limit check (light.cpp:45), which for a point
+	// light at distance D fires at hit k when D - t_k - (t_k - t_{k-1}) <= 0, i.e. never while
+	// t_k <= D/2, and never for a directional light (light.cpp:60).  Every other way out of the loop
+	// before that surface (light.cpp:47-48) returns 0, and so does the surface itself.  So a
+	// non-transmissive entry at t <= sure_t (0.49 D, or infinity) settles the result whatever else
+	// the ray meets: no need to collect the hits in front of it.
+	if (term && !inside && t <= B.sure_t) { B.dead = true; B.cut = t; return; }
 	int pos = B.n;
 	while (pos > 0 && key_less(t, key, B.h[pos - 1].t, B.h[pos - 1].key)) pos--;
 	if (B.n == RT_SHADOW_K) {

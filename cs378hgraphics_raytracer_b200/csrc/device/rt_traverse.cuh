@@ -255,6 +255,8 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 						}
 					} else {
 						emit_face(S, V.obj, (unsigned)V.rank, pos, V.len, o, d, dw, B);
+						if (B.dead) { sp = 0; break; } // any-hit exit (rt_shadow.cuh), through the pop section's one way out: a second
+						                               // return inside the loop costs the warp its reconvergence points (3x slower)
 						lim = lim_to_local(B.cut, V.len);
 					}
 				}
@@ -305,6 +307,8 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 						if (C.have) lim = C.best_t;
 					} else {
 						prim_list(S, ob, L, dw, rank, B);
+						if (B.dead) { sp = 0; break; } // any-hit exit (rt_shadow.cuh), through the pop section's one way out: a second
+						                               // return inside the loop costs the warp its reconvergence points (3x slower)
 						lim = B.cut;
 					}
 				}
@@ -400,10 +404,13 @@ RT_COLD void shadow_begin(ShadowState& st, SBuf& B, const rt_light& Lt, const d3
 	st.point = Lt.type != RT_LIGHT_DIRECTIONAL;
 	st.limit = RT_T_INF;
 	// area and spot lights: the limit check is against the ray's impact point on the light's plane
-	// (light.cpp:91-99), no distance bound is used for culling
+	// (light.cpp:91-99), no distance bound is used for culling and no any-hit exit is taken
+	B.sure_t = Lt.type == RT_LIGHT_DIRECTIONAL ? RT_T_INF : -1.0;
+	B.dead = false;
 	if (Lt.type == RT_LIGHT_POINT) {
 		const double D = length(ld3(Lt.position) - pos);
 		st.limit = D * (1.0 + 1e-9) + 1e-9;
+		B.sure_t = 0.49 * D;
 	}
 	st.sattn = mk3(1.0, 1.0, 1.0);
 	st.last_t = 0.0;
@@ -421,6 +428,7 @@ RT_HD void shadow_pass_reset(const ShadowState& st, SBuf& B)
 // when another pass (continuing after B.floor) is needed.
 RT_COLD bool shadow_walk(ShadowState& st, SBuf& B, const rt_light& Lt, const d3& dir, const rt_params& prm)
 {
+	if (B.dead) { st.sattn = mk3(0.0, 0.0, 0.0); return true; }
 	const bool overflow = B.min_dropped < RT_T_INF && B.min_dropped <= B.cut;
 	const bool aterm = prm.aterm_thresh > 0.0;
 	const d3 lpos = ld3(Lt.position);

@@ -41,7 +41,8 @@ struct rt_ctx {
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
 	unsigned long long* pinned = nullptr;  // round counters read back by the host
 	cudaEvent_t ev_round = nullptr;
-	cudaStream_t stream2 = nullptr;        // shadow rays of round r overlap round r+1's closest-hit work
+	cudaStream_t stream2[2] = {nullptr, nullptr}; // shadow rays of round r (stream r & 1) overlap round r+1's closest-hit work AND the
+	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
 	unsigned long long rounds = 0;
@@ -165,7 +166,6 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if ((st = make_queue(ctx, B_SQ2_D, B_SQ2_I, W * (L > 0 ? L : 1), 9, sq[1])) != RT_OK) return st;
 	// per-stage profiling wants clean kernel times: no overlap then
 	const bool overlap = ctx->overlap && !ctx->profile;
-	cudaStream_t sstream = overlap ? ctx->stream2 : ctx->stream;
 	bool shadow_pending[2] = {false, false};
 	long long round = 0;
 	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
@@ -211,18 +211,20 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		}
 		if (m == 0) break;
 		const int par = (int)(round & 1);
-		// this parity's shadow queue is free once the shadow kernel of two rounds ago is done
-		if (shadow_pending[par] && overlap) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_shadow[par], 0));
-		shadow_pending[par] = false;
 		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
-		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt));
 		if (ctx->walk_budget > 0)
 			STAGE(RT_STAGE_COOP, k_wave_closest_heavy<<<ctx->sm_count * 4 * (2 / RT_COOP_WARPS), 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt));
+		// this parity's shadow queue is free once the shadow kernel of two rounds ago is done; only the
+		// shade stage writes it, so the closest-hit walks above did not have to wait
+		if (shadow_pending[par] && overlap) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_shadow[par], 0));
+		shadow_pending[par] = false;
+		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
 		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		if (L > 0) {
+			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
 			if (overlap) {
 				CK(cudaEventRecord(ctx->ev_shade[par], ctx->stream));
 				CK(cudaStreamWaitEvent(sstream, ctx->ev_shade[par], 0));
@@ -320,7 +322,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	cudaEventCreate(&ctx->ev0);
 	cudaEventCreate(&ctx->ev1);
 	cudaEventCreateWithFlags(&ctx->ev_round, cudaEventDisableTiming);
-	cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
+	for (int k = 0; k < 2; k++) cudaStreamCreateWithFlags(&ctx->stream2[k], cudaStreamNonBlocking);
 	for (int k = 0; k < 2; k++) { cudaEventCreateWithFlags(&ctx->ev_shade[k], cudaEventDisableTiming); cudaEventCreateWithFlags(&ctx->ev_shadow[k], cudaEventDisableTiming); }
 	if (const char* e = getenv("RT_B200_OVERLAP")) ctx->overlap = atoi(e) != 0;
 	if (cudaMallocHost((void**)&ctx->pinned, 64) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
@@ -350,7 +352,8 @@ void rt_destroy(rt_ctx* ctx)
 	if (ctx->pinned) cudaFreeHost(ctx->pinned);
 	if (ctx->ev_round) cudaEventDestroy(ctx->ev_round);
 	for (int k = 0; k < 2; k++) { if (ctx->ev_shade[k]) cudaEventDestroy(ctx->ev_shade[k]); if (ctx->ev_shadow[k]) cudaEventDestroy(ctx->ev_shadow[k]); }
-	if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+	for (int k = 0; k < 2; k++)
+		if (ctx->stream2[k]) cudaStreamDestroy(ctx->stream2[k]);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);

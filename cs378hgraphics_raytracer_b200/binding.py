@@ -40,7 +40,8 @@ class Params(ctypes.Structure):
 class Stats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint64) for n in "camera_rays reflection_rays refraction_rays shadow_rays".split()] + \
                [("device_ms", ctypes.c_double), ("launches", ctypes.c_uint64), ("cooperative_rays", ctypes.c_uint64),
-                ("rounds", ctypes.c_uint64), ("stage_ms", ctypes.c_double * 6), ("stage_launches", ctypes.c_uint64 * 6)]
+                ("rounds", ctypes.c_uint64), ("stage_ms", ctypes.c_double * 6), ("stage_launches", ctypes.c_uint64 * 6),
+                ("culled_shadow_rays", ctypes.c_uint64)]
 
     STAGES = ("gen", "closest", "coop", "shade", "shadow", "other")
 

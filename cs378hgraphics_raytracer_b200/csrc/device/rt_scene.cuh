@@ -86,6 +86,8 @@ struct DScene {
 	double scene_slack; // pruning slack of the scene-level tree (world space)
 	int32_t n_lights;
 	int32_t n_objs;
+	int32_t kt_unit; // every material's kt lies in [0,1]^3 (texels always do): shadow attenuations are finite
+	int32_t pad_;
 };
 
 // A ray plus what traversal derives from it once.

@@ -65,7 +65,7 @@ struct HitQueue {
 
 // device-side counters of one trace call
 struct WaveCounters {
-	unsigned long long stats[8]; // camera, reflection, refraction, shadow rays, overflow flag, heavy rays
+	unsigned long long stats[8]; // camera, reflection, refraction, shadow rays, overflow flag, heavy rays, culled shadow rays
 	unsigned long long n_children;
 	unsigned long long n_heavy;      // rays of this round that exhausted the node budget
 	unsigned long long heavy_cursor; // next heavy ray to be taken by a warp
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 		sample = Q.i[q];
 		if (((meta >> 12) & 15) == KIND_DEAD) live = false;
 	}
-	unsigned n_cam = 0, n_refl = 0, n_refr = 0, n_shadow = 0, overflow = 0;
+	unsigned n_cam = 0, n_refl = 0, n_refr = 0, n_shadow = 0, n_culled = 0, overflow = 0;
 	bool lit = false, has_refl = false, has_refr = false;
 	RayTask kid[2];
 	MatEval me;
@@ -250,15 +250,26 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 		for (int li = 0; li < S.n_lights; li++) {
 			const rt_light& Lt = S.lights[li];
 			if (!light_is_area(Lt)) {
-				const long long s = wave_reserve(lit, lt_mask, &cnt->n_shadow[parity]);
-				if (s >= 0) {
-					n_shadow++;
-					if (s >= SQ.cap) { overflow = 1; continue; }
-					d3 term, pb, sdir;
+				// Material::shade adds dattn * sattn * colour * (d_comp + s_comp) (material.cpp:64).  Where
+				// the weighted Phong term is exactly (0,0,0) - the light is behind the surface - the sum
+				// gains 0 whatever the shadow ray finds (sattn is finite: DScene::kt_unit), so the ray is
+				// counted, as the reference counts it, but never walked.
+				d3 wterm = mk3(0, 0, 0), pb = mk3(0, 0, 0), sdir = mk3(0, 0, 1);
+				bool walk = false;
+				if (lit) {
+					d3 term;
 					light_term(Lt, me, hitP, h.N, rd, term, pb, sdir);
+					wterm = w * term;
+					walk = !(S.kt_unit && wterm.x == 0.0 && wterm.y == 0.0 && wterm.z == 0.0);
+					n_shadow++;
+					if (!walk) n_culled++;
+				}
+				const long long s = wave_reserve(walk, lt_mask, &cnt->n_shadow[parity]);
+				if (s >= 0) {
+					if (s >= SQ.cap) { overflow = 1; continue; }
 					SQ.store_v(0, s, pb);
 					SQ.store_v(3, s, sdir);
-					SQ.store_v(6, s, w * term);
+					SQ.store_v(6, s, wterm);
 					SQ.store_meta(s, sample, li);
 				}
 				continue;
@@ -293,6 +304,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 		n_refl += __shfl_down_sync(0xffffffffu, n_refl, o);
 		n_refr += __shfl_down_sync(0xffffffffu, n_refr, o);
 		n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
+		n_culled += __shfl_down_sync(0xffffffffu, n_culled, o);
 		overflow |= __shfl_down_sync(0xffffffffu, overflow, o);
 	}
 	if (lane == 0) {
@@ -300,6 +312,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 		if (n_refl) atomicAdd(cnt->stats + 1, (unsigned long long)n_refl);
 		if (n_refr) atomicAdd(cnt->stats + 2, (unsigned long long)n_refr);
 		if (n_shadow) atomicAdd(cnt->stats + 3, (unsigned long long)n_shadow);
+		if (n_culled) atomicAdd(cnt->stats + 6, (unsigned long long)n_culled);
 		if (overflow) atomicAdd(cnt->stats + 4, 1ull);
 	}
 }

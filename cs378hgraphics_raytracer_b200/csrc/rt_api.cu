@@ -291,6 +291,7 @@ rt_status read_stats(rt_ctx* ctx, rt_stats* stats, float ms)
 		stats->device_ms = ms;
 		stats->launches = ctx->launches;
 		stats->cooperative_rays = h[5];
+		stats->culled_shadow_rays = h[6];
 		stats->rounds = ctx->rounds;
 		for (int k = 0; k < 6; k++) { stats->stage_ms[k] = 0.0; stats->stage_launches[k] = 0; }
 		for (const rt_ctx::Span& sp : ctx->spans) {
@@ -499,6 +500,16 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	S.stree.node_off = 0;
 	S.n_lights = (int)A.count(RT_SEC_LIGHTS);
 	S.n_objs = (int)A.count(RT_SEC_OBJECTS);
+	// k_wave_shade may drop a shadow ray whose Phong term is exactly 0 only if 0 * attenuation is 0,
+	// i.e. the attenuation (a product of kt ^ distance) cannot be inf or NaN
+	S.kt_unit = 1;
+	S.pad_ = 0;
+	{
+		const rt_material* hm = A.ptr<rt_material>(RT_SEC_MATERIALS);
+		for (size_t i = 0; i < A.count(RT_SEC_MATERIALS); i++)
+			for (int c = 0; c < 3; c++)
+				if (!(hm[i].k[RT_KT][c] >= 0.0 && hm[i].k[RT_KT][c] <= 1.0)) S.kt_unit = 0;
+	}
 	unsigned hflags[3];
 	CK(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream)); // also: the caller may reuse `arena` on return

@@ -89,6 +89,8 @@ typedef struct rt_stats {
 	 * after rt_set_profiling(ctx, 1).  Stages: RT_STAGE_* below. */
 	double stage_ms[6];
 	uint64_t stage_launches[6];
+	uint64_t culled_shadow_rays; /* of shadow_rays: counted as the reference counts them but not walked, because
+	                                their Phong term (light.cpp's caller, material.cpp:50-65) is exactly 0 */
 } rt_stats;
 enum { RT_STAGE_GEN = 0, RT_STAGE_CLOSEST = 1, RT_STAGE_COOP = 2, RT_STAGE_SHADE = 3, RT_STAGE_SHADOW = 4, RT_STAGE_OTHER = 5 };
 

@@ -239,6 +239,36 @@ def test_cooperative_walk_same_frame(rtlib, oracle_mod, scene_dir, scene, monkey
         c.close()
 
 
+def test_zero_term_shadow_rays_are_counted_not_walked(rtlib, oracle_mod, scene_dir, tmp_path):
+    """A shadow ray whose Phong term is exactly 0 (light behind the surface) cannot change the pixel:
+    k_wave_shade counts it, as the reference does, but does not queue it - provided every kt lies in
+    [0,1] so that the attenuation is finite.  With a kt > 1 in the scene nothing is dropped.  Either
+    way the frame and the ray counts are the reference's."""
+    src = (scene_dir / "prims_mixed.ray").read_text()
+    odd = tmp_path / "prims_kt_gt1.ray"
+    assert "transmissive=(0.5,0.5,0.7)" in src
+    odd.write_text(src.replace("transmissive=(0.5,0.5,0.7)", "transmissive=(0.5,1.25,0.7)"))
+    for path, expect_cull in ((scene_dir / "prims_mixed.ray", True), (scene_dir / "dragon_small.ray", True), (odd, False)):
+        c = rtlib.Context(0)
+        try:
+            c.upload(rtlib.load_ray_file(str(path)))
+            orc = oracle_mod.Oracle(str(path))
+            w = 240
+            h = oracle_mod.frame_height(w, orc.aspect)
+            p = rtlib.Params.default(depth=5)
+            ref_img, ref_st, _ = orc.render(p, w, h)
+            img, st = c.render(p, w, h)
+            d = oracle_mod.image_diff(ref_img, img)
+            assert d["within1"] >= TOL_WITHIN1, (str(path), d)
+            assert abs(int(st.shadow_rays) - int(ref_st.shadow_rays)) <= max(2, 1e-3 * ref_st.shadow_rays)
+            if expect_cull:
+                assert 0 < st.culled_shadow_rays < st.shadow_rays
+            else:
+                assert st.culled_shadow_rays == 0
+        finally:
+            c.close()
+
+
 @pytest.mark.parametrize("scene", SCENES)
 def test_device_built_layouts_match_host(rtlib, ctx, scene_dir, scene):
     """rt_upload_scene builds the wide nodes / triangle records / tree descriptors with device

@@ -59,6 +59,16 @@ struct WorkScope {
 #define RT_WORK_SCOPE(m) ((void)0)
 #endif
 
+// 1-based index of the lowest set bit
+RT_HD int rt_ffs(unsigned v)
+{
+#ifdef __CUDA_ARCH__
+	return __ffs((int)v);
+#else
+	return __builtin_ffs((int)v);
+#endif
+}
+
 struct TravClosest {
 	bool have;
 	double best_t;
@@ -261,19 +271,31 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 					}
 				}
 			} else {
+				// two passes over the leaf's (at most three) candidates: first the box tests of all of
+				// them, then the object-space tests of the survivors.  The lanes of a warp that have ANY
+				// survivor then run the long primitive code together, instead of only those whose i-th
+				// candidate survived.  Postponing a test can only weaken the distance cull, never the result.
+				unsigned pend = 0;
 #pragma unroll 1
 				for (int i = 0; i < count; i++) {
-					const int rank = first + i;
-					const DItemBox& ib = S.sboxf[rank];
+					const DItemBox& ib = S.sboxf[first + i];
 					RT_CNT(objs, mode);
 					if (box_miss_f(ib, F)) continue;
-					const int obj = ib.obj;
-					const rt_object& ob = S.objs[obj];
+					const rt_object& ob = S.objs[ib.obj];
 					// Geometry::intersect / intersectList: world-bbox pretest (scene.cpp:15,43) is a real
 					// filter (leaf boxes are unions), then the object-space test
 					double eb;
 					if (!box_hit(ob.bbox, ob.bbox + 3, o, d, I, eb)) continue;
 					if (prune && eb > lim) continue;
+					pend |= 1u << i;
+				}
+#pragma unroll 1
+				while (pend) {
+					const int i = rt_ffs(pend) - 1;
+					pend &= pend - 1;
+					const int rank = first + i;
+					const int obj = S.sboxf[rank].obj;
+					const rt_object& ob = S.objs[obj];
 					LocalRay L;
 					to_local(L, ob, o, d);
 					if (ob.type == RT_OBJ_TRIMESH) {

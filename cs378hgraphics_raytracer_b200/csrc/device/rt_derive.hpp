@@ -75,6 +75,16 @@ inline void nodes_to_float(const std::vector<DNode2>& in, std::vector<DNode2f>& 
 	}
 }
 
+// DScene::kt_unit: every constant kt lies in [0,1]^3 (texels always do), so a shadow attenuation - a
+// product of kt ^ distance - is finite and 0 * attenuation is exactly 0
+inline int kt_all_unit(const rt_material* m, uint64_t cnt)
+{
+	for (uint64_t i = 0; i < cnt; i++)
+		for (int c = 0; c < 3; c++)
+			if (!(m[i].k[RT_KT][c] >= 0.0 && m[i].k[RT_KT][c] <= 1.0)) return 0;
+	return 1;
+}
+
 inline double box_extent(const rt_node& n)
 {
 	double m = 1.0;

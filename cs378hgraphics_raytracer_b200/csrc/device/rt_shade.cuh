@@ -127,6 +127,8 @@ RT_HD d3 shade(const DScene& S, const rt_params& prm, const MatEval& m, const d3
 		light_term(L, m, P, h.N, d, term, pb, sdir);
 		if (!light_is_area(L)) {
 			shadow_rays++;
+			// a term of exactly 0 gains 0 whatever the shadow ray finds (finite attenuation): counted, not walked
+			if (S.kt_unit && term.x == 0.0 && term.y == 0.0 && term.z == 0.0) continue;
 			const d3 sattn = shadow_attenuation(S, L, pb, sdir, prm);
 			out = out + sattn * term;
 			continue;

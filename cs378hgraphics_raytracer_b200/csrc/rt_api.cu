@@ -502,14 +502,8 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	S.n_objs = (int)A.count(RT_SEC_OBJECTS);
 	// k_wave_shade may drop a shadow ray whose Phong term is exactly 0 only if 0 * attenuation is 0,
 	// i.e. the attenuation (a product of kt ^ distance) cannot be inf or NaN
-	S.kt_unit = 1;
+	S.kt_unit = kt_all_unit(A.ptr<rt_material>(RT_SEC_MATERIALS), A.count(RT_SEC_MATERIALS));
 	S.pad_ = 0;
-	{
-		const rt_material* hm = A.ptr<rt_material>(RT_SEC_MATERIALS);
-		for (size_t i = 0; i < A.count(RT_SEC_MATERIALS); i++)
-			for (int c = 0; c < 3; c++)
-				if (!(hm[i].k[RT_KT][c] >= 0.0 && hm[i].k[RT_KT][c] <= 1.0)) S.kt_unit = 0;
-	}
 	unsigned hflags[3];
 	CK(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream)); // also: the caller may reuse `arena` on return

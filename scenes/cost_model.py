@@ -72,7 +72,9 @@ def main():
             hist = [int(x) for x in buf[m, 4:36]]
             while hist and hist[-1] == 0:
                 hist.pop()
-            rays = int(n_rays[m])
+            # per WALKED ray: shadow rays with an exactly zero Phong term are counted but never walked
+            # (rt_shade.cuh), bench.py multiplies these figures by the walked rays only
+            rays = min(int(n_rays[m]), walks)
             n_box = walks + 2 * nodes
             kb = n_box * BOX_B + tris * TRI_B + objs * OBJ_B + rays * RAY_B
             kf = n_box * BOX_F + tris * TRI_F + objs * (OBJ_F + XFORM_F) + (rays * SHADE_F if m == 1 else 0)

@@ -52,6 +52,8 @@ void setup(Sim& sim, const void* arena)
 	S.scene_slack = sim.D.scene_slack;
 	S.n_lights = (int)A.count(RT_SEC_LIGHTS);
 	S.n_objs = (int)A.count(RT_SEC_OBJECTS);
+	S.kt_unit = kt_all_unit(A.ptr<rt_material>(RT_SEC_MATERIALS), A.count(RT_SEC_MATERIALS));
+	S.pad_ = 0;
 }
 
 template <bool PRUNE> d3 trace_tree(const DScene& S, const rt_params& prm, const RayTask& root, rt_stats* st)

@@ -106,6 +106,10 @@ def lib():
     L.rt_arena_free.restype = None
     L.rt_host_last_error.restype = cp
     L.rt_arena_validate.argtypes = [vp, sz]
+    L.rt_write_image.argtypes = [cp, ctypes.c_int, ctypes.c_int, vp]
+    L.rt_write_image.restype = i32
+    L.rt_read_image.argtypes = [cp, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), ctypes.POINTER(vp)]
+    L.rt_read_image.restype = i32
     for f in ("rt_create", "rt_upload_scene", "rt_render", "rt_render_tiles", "rt_render_device", "rt_trace_pixels",
               "rt_trace_rays", "rt_load_ray_file", "rt_arena_validate"):
         getattr(L, f).restype = i32
@@ -165,6 +169,27 @@ def load_ray_file(path, cubemap_faces=None):
     if st != 0:
         raise RtError(st, L.rt_host_last_error().decode(errors="replace"))
     return Arena(p.value, n.value)
+
+
+def write_image(path, img):
+    """writeImage (images.cc:58-66): img is (h, w, 3) uint8 with row 0 = bottom scan line; .png or .bmp by extension."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w, _ = img.shape
+    st = lib().rt_write_image(os.fsencode(path), w, h, img.ctypes.data_as(ctypes.c_void_p))
+    if st != 0:
+        raise RtError(st, "could not write " + str(path))
+
+
+def read_image(path):
+    """readImage (images.cc:48-55): (h, w, 3) uint8, row 0 = bottom scan line."""
+    w, h, p = ctypes.c_int(), ctypes.c_int(), ctypes.c_void_p()
+    st = lib().rt_read_image(os.fsencode(path), ctypes.byref(w), ctypes.byref(h), ctypes.byref(p))
+    if st != 0:
+        raise RtError(st, "could not read " + str(path))
+    try:
+        return np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_uint8)), (h.value, w.value, 3)).copy()
+    finally:
+        lib().rt_arena_free(p)
 
 
 class Context:

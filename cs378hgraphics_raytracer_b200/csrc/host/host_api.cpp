@@ -148,4 +148,24 @@ static rt_status validate_impl(const void* arena, size_t bytes, bool deep)
 	return RT_OK;
 }
 
+rt_status rt_write_image(const char* path, int w, int h, const uint8_t* rgb)
+{
+	if (!path || !rgb || w <= 0 || h <= 0) return RT_ERR_ARG;
+	return rs::write_image(path, w, h, rgb) ? RT_OK : RT_ERR_IO;
+}
+
+rt_status rt_read_image(const char* path, int* w, int* h, uint8_t** rgb_out)
+{
+	if (!path || !w || !h || !rgb_out) return RT_ERR_ARG;
+	rs::Texture t;
+	if (!rs::read_image(path, t)) return RT_ERR_IO;
+	uint8_t* p = (uint8_t*)std::malloc(t.rgb.size() ? t.rgb.size() : 1);
+	if (!p) return RT_ERR_IO;
+	std::memcpy(p, t.rgb.data(), t.rgb.size());
+	*w = t.width;
+	*h = t.height;
+	*rgb_out = p;
+	return RT_OK;
+}
+
 } // extern "C"

@@ -1,7 +1,7 @@
 // main_cli.cpp - `ray_b200`: the reference's command line (ui/CommandLineUI.cpp:25-147) in front of
 // the device path.  Same options and option grammar (-O <mode> followed by -A/-B/-C values):
-//   ray_b200 [-r depth] [-w width] [-c cubemap_file] [-O a|j|r|o|d|g|c|s] [-A v] [-B v] [-C v] in.ray out.bmp
-// The output is a 24-bit BMP (libpng is not on this image); -j (json settings) and -t are not mirrored.
+//   ray_b200 [-r depth] [-w width] [-c cubemap_file] [-O a|j|r|o|d|g|c|s] [-A v] [-B v] [-C v] in.ray out.png|out.bmp
+// The output format follows the extension as the reference's writeImage does (PNG through zlib, else BMP); -j (json settings) and -t are not mirrored.
 #include <dirent.h>
 #include <unistd.h>
 #include <chrono>
@@ -11,11 +11,10 @@
 #include <vector>
 #include "RayTracer.h"
 
-namespace rs { bool write_bmp24(const std::string& path, int w, int h, const unsigned char* rgb); }
 
 static void usage(const char* prog)
 {
-	std::fprintf(stderr, "usage: %s [options] [input.ray output.bmp]\n"
+	std::fprintf(stderr, "usage: %s [options] [input.ray output.png|output.bmp]\n"
 	                     "  -r <#>      set recursion level (default 0)\n"
 	                     "  -w <#>      set output image width (default 150)\n"
 	                     "  -c <file>   one of the six cubemap images (the others are found next to it)\n"
@@ -107,7 +106,7 @@ int main(int argc, char** argv)
 	const auto t1 = std::chrono::steady_clock::now();
 	unsigned char* buf;
 	tracer.getBuffer(buf, width, height);
-	if (buf && !rs::write_bmp24(img_name, width, height, buf)) { std::fprintf(stderr, "could not write %s\n", img_name); return 1; }
+	if (buf && rt_write_image(img_name, width, height, buf) != RT_OK) { std::fprintf(stderr, "could not write %s\n", img_name); return 1; }
 	const rt_stats& s = tracer.lastStats();
 	const double rays = (double)(s.camera_rays + s.reflection_rays + s.refraction_rays + s.shadow_rays);
 	std::printf("total time = %.6f seconds, rays traced = %.0f, device time = %.3f ms (%.1f Mrays/s)\n",

@@ -748,7 +748,7 @@ int load_texture(Scene& sc, const std::string& path)
 	auto it = sc.texture_cache.find(path);
 	if (it != sc.texture_cache.end()) return it->second;
 	Texture t;
-	if (!read_bmp24(path, t)) throw std::runtime_error("Texture mapping exception: Unable to load texture map '" + path + "'.");
+	if (!read_image(path, t)) throw std::runtime_error("Texture mapping exception: Unable to load texture map '" + path + "'.");
 	sc.textures.push_back(std::move(t));
 	int id = (int)sc.textures.size() - 1;
 	sc.texture_cache[path] = id;

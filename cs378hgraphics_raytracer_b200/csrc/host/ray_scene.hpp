@@ -107,6 +107,8 @@ struct Scene {
 void parse_ray_file(const std::string& path, Scene& out);
 // image_io.cpp
 bool read_bmp24(const std::string& path, Texture& out);
+bool read_image(const std::string& path, Texture& out);  // by extension: .png or .bmp (image_io.cpp)
+bool write_image(const std::string& path, int w, int h, const unsigned char* rgb);
 int load_texture(Scene& sc, const std::string& path); // cached; throws on failure
 
 // scene_flatten.cpp: tree build (kdTree.h:23-78) + arena (include/rt_arena.h); malloc'ed

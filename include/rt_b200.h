@@ -161,6 +161,15 @@ const char* rt_host_last_error(void);
 /* Checks magic, version, section table and index ranges of an arena. */
 rt_status rt_arena_validate(const void* arena, size_t bytes);
 
+/* ---- output stage (no GPU needed) -------------------------------------------------------- */
+/* Replaces writeImage (reference fileio/images.cc:58-66 -> writePNG pngimage.cpp:226-285, writeBMP
+ * bitmap.cpp:95-140): chosen by extension, case-insensitive, ".png" = 8-bit RGB PNG, anything else =
+ * 24-bit BMP.  rgb is the frame as rt_render returns it (w*h*3, row 0 = bottom scan line). */
+rt_status rt_write_image(const char* path, int w, int h, const uint8_t* rgb);
+/* Replaces readImage (images.cc:48-55): w*h*3 bytes, row 0 = bottom scan line, malloc'ed (free with
+ * rt_arena_free).  .bmp (24 bit) and .png (8-bit RGB, non-interlaced, no gAMA chunk) are read. */
+rt_status rt_read_image(const char* path, int* w, int* h, uint8_t** rgb_out);
+
 #ifdef __cplusplus
 }
 #endif

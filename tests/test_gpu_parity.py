@@ -320,6 +320,12 @@ def test_cli_renders_reference_frame(rtlib, oracle_mod, scene_dir, tmp_path):
     ref_img, _, _ = orc.render(rtlib.Params.default(depth=5), w, h)
     d = oracle_mod.image_diff(ref_img, px)
     assert d["within1"] >= TOL_WITHIN1, d
+    # the same frame as PNG (the reference CLI's usual output, writeImage -> writePNG)
+    out_png = tmp_path / "o.png"
+    r = subprocess.run([exe, "-r", "5", "-w", "200", str(path), str(out_png)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert out_png.read_bytes()[:4] == b"\x89PNG"
+    assert np.array_equal(rtlib.read_image(str(out_png)), px)
 
 
 GOLDEN = {"hitchcock": "hitchcock.ray", "trimesh2": "trimesh2.ray", "dragon_small": "dragon_small.ray", "prims_mixed": "prims_mixed.ray",

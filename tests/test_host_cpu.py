@@ -219,3 +219,54 @@ def test_golden_vectors_hostsim(rtlib, hostsim, scene_dir, name):
     d = np.abs(img.astype(np.int32) - g["frame"].astype(np.int32)).max(axis=2)
     assert (d <= 1).mean() >= 0.999
     assert [st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays] == [int(x) for x in g["counts"]]
+
+
+def test_png_and_bmp_output_stage(rtlib, tmp_path):
+    """rt_write_image / rt_read_image (writeImage / readImage, images.cc:48-66; writePNG pngimage.cpp:226-285):
+    the PNG is decoded by an independent reader (Pillow) and must be the frame with its rows flipped
+    (buffer row 0 = bottom scan line = last row of the file); a PNG written by Pillow with its own
+    adaptive scan-line filters must be read back the same way; BMP round trip; unknown extension -> BMP."""
+    from PIL import Image
+    rng = np.random.default_rng(3)
+    h, w = 37, 53  # odd sizes: BMP row padding, PNG filter edge cases
+    img = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+    img[5:20, 10:40] = np.linspace(0, 255, 30, dtype=np.uint8)[None, :, None]  # smooth part: Pillow picks Sub/Up/Paeth here
+    png = tmp_path / "o.PNG"
+    rtlib.write_image(str(png), img)
+    with Image.open(png) as im:
+        assert im.mode == "RGB" and im.size == (w, h)
+        assert np.array_equal(np.asarray(im), img[::-1])
+    assert np.array_equal(rtlib.read_image(str(png)), img)
+    theirs = tmp_path / "pil.png"
+    Image.fromarray(img[::-1]).save(theirs, optimize=True)
+    assert np.array_equal(rtlib.read_image(str(theirs)), img)
+    bmp = tmp_path / "o.bmp"
+    rtlib.write_image(str(bmp), img)
+    assert bmp.read_bytes()[:2] == b"BM"
+    assert np.array_equal(rtlib.read_image(str(bmp)), img)
+    odd = tmp_path / "o.xyz"
+    rtlib.write_image(str(odd), img)
+    assert odd.read_bytes()[:2] == b"BM"
+    # what the reference would read differently is refused, not guessed
+    Image.fromarray(np.dstack([img[::-1], np.full((h, w), 200, np.uint8)])).save(tmp_path / "rgba.png")
+    with pytest.raises(rtlib.RtError):
+        rtlib.read_image(str(tmp_path / "rgba.png"))
+
+
+def test_raycheck_tool(rtlib, tmp_path):
+    """raycheck.py:21-34's RMS criterion and quickdiff's diff / montage images over the library's image I/O."""
+    from cs378hgraphics_raytracer_b200 import raycheck
+    rng = np.random.default_rng(5)
+    ref = rng.integers(0, 256, size=(24, 40, 3), dtype=np.uint8)
+    img = ref.copy()
+    img[3, 7, 1] = np.uint8(int(ref[3, 7, 1]) ^ 1)  # one channel off by one
+    r = raycheck.compare(img, ref)
+    assert r["within1"] == 1.0 and r["max_abs"] == 1 and 0 < r["rms"] < 0.1
+    assert r["rms_u8"] >= r["rms"]  # the reference's uint8 subtraction can only overstate
+    rtlib.write_image(str(tmp_path / "a.png"), img)
+    rtlib.write_image(str(tmp_path / "b.png"), ref)
+    assert raycheck.main([str(tmp_path / "a.png"), str(tmp_path / "b.png"), "--diff", str(tmp_path / "d.png"), "--montage", str(tmp_path / "m.bmp")]) == 0
+    assert rtlib.read_image(str(tmp_path / "d.png")).sum() == 1
+    m = rtlib.read_image(str(tmp_path / "m.bmp"))
+    assert m.shape == (24, 120, 3) and np.array_equal(m[:, 40:80], ref)
+    assert raycheck.main([str(tmp_path / "a.png"), str(tmp_path / "b.png"), "--maxrms", "0.0001"]) == 1

@@ -106,6 +106,10 @@ def lib():
     L.rt_arena_free.restype = None
     L.rt_host_last_error.restype = cp
     L.rt_arena_validate.argtypes = [vp, sz]
+    L.rt_arena_save.argtypes = [cp, vp, sz]
+    L.rt_arena_save.restype = i32
+    L.rt_arena_load.argtypes = [cp, ctypes.POINTER(vp), ctypes.POINTER(sz)]
+    L.rt_arena_load.restype = i32
     L.rt_write_image.argtypes = [cp, ctypes.c_int, ctypes.c_int, vp]
     L.rt_write_image.restype = i32
     L.rt_read_image.argtypes = [cp, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), ctypes.POINTER(vp)]
@@ -168,6 +172,22 @@ def load_ray_file(path, cubemap_faces=None):
     st = L.rt_load_ray_file(os.fsencode(path), cm, ctypes.byref(p), ctypes.byref(n))
     if st != 0:
         raise RtError(st, L.rt_host_last_error().decode(errors="replace"))
+    return Arena(p.value, n.value)
+
+
+def save_arena(path, arena):
+    """Writes the flattened scene to a cache file (rt_arena_save)."""
+    st = lib().rt_arena_save(os.fsencode(path), ctypes.c_void_p(arena.ptr), arena.nbytes)
+    if st != 0:
+        raise RtError(st, "could not save the arena to " + str(path))
+
+
+def load_arena(path):
+    """Reads a cache file written by save_arena (rt_arena_load: validated, refused if stale or damaged)."""
+    p, n = ctypes.c_void_p(), ctypes.c_size_t()
+    st = lib().rt_arena_load(os.fsencode(path), ctypes.byref(p), ctypes.byref(n))
+    if st != 0:
+        raise RtError(st, "could not load an arena from " + str(path))
     return Arena(p.value, n.value)
 
 

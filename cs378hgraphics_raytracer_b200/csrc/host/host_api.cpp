@@ -1,5 +1,6 @@
 // host_api.cpp - the host-only half of the C-ABI (include/rt_b200.h): scene loading, arena
 // validation, default settings.  No CUDA here; the device half is ../rt_api.cu.
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
@@ -145,6 +146,36 @@ static rt_status validate_impl(const void* arena, size_t bytes, bool deep)
 	const int32_t* vm = A.ptr<int32_t>(RT_SEC_VMATS);
 	for (uint64_t k = 0; deep && k < A.count(RT_SEC_VMATS); k++)
 		if (vm[k] < 0 || (uint64_t)vm[k] >= n_mat) return RT_ERR_ARG;
+	return RT_OK;
+}
+
+rt_status rt_arena_save(const char* path, const void* arena, size_t bytes)
+{
+	if (!path || rt_arena_validate_tables(arena, bytes) != RT_OK) return RT_ERR_ARG;
+	FILE* f = std::fopen(path, "wb");
+	if (!f) return RT_ERR_IO;
+	const bool ok = std::fwrite(arena, 1, bytes, f) == bytes;
+	return (std::fclose(f) == 0 && ok) ? RT_OK : RT_ERR_IO;
+}
+
+rt_status rt_arena_load(const char* path, void** arena_out, size_t* bytes_out)
+{
+	if (!path || !arena_out || !bytes_out) return RT_ERR_ARG;
+	*arena_out = nullptr;
+	*bytes_out = 0;
+	FILE* f = std::fopen(path, "rb");
+	if (!f) return RT_ERR_IO;
+	rt_arena_header h;
+	if (std::fread(&h, 1, sizeof(h), f) != sizeof(h) || h.magic != RT_ARENA_MAGIC || h.version != RT_ARENA_VERSION || h.total_bytes < sizeof(h)) { std::fclose(f); return RT_ERR_ARG; }
+	void* p = std::aligned_alloc(RT_ARENA_ALIGN, (h.total_bytes + RT_ARENA_ALIGN - 1) / RT_ARENA_ALIGN * RT_ARENA_ALIGN);
+	if (!p) { std::fclose(f); return RT_ERR_IO; }
+	std::memcpy(p, &h, sizeof(h));
+	const size_t rest = h.total_bytes - sizeof(h);
+	const bool ok = std::fread((char*)p + sizeof(h), 1, rest, f) == rest && std::fgetc(f) == EOF;
+	std::fclose(f);
+	if (!ok || rt_arena_validate(p, h.total_bytes) != RT_OK) { std::free(p); return RT_ERR_ARG; }
+	*arena_out = p;
+	*bytes_out = h.total_bytes;
 	return RT_OK;
 }
 

@@ -161,6 +161,12 @@ const char* rt_host_last_error(void);
 /* Checks magic, version, section table and index ranges of an arena. */
 rt_status rt_arena_validate(const void* arena, size_t bytes);
 
+/* Cached binary scene: the arena is one position-independent block, so the cache
+ * file IS the arena.  rt_arena_load reads the file into a malloc'ed block (rt_arena_free) and runs
+ * rt_arena_validate on it; a file of another arena version, a truncated or a corrupted one is refused. */
+rt_status rt_arena_save(const char* path, const void* arena, size_t bytes);
+rt_status rt_arena_load(const char* path, void** arena_out, size_t* bytes_out);
+
 /* ---- output stage (no GPU needed) -------------------------------------------------------- */
 /* Replaces writeImage (reference fileio/images.cc:58-66 -> writePNG pngimage.cpp:226-285, writeBMP
  * bitmap.cpp:95-140): chosen by extension, case-insensitive, ".png" = 8-bit RGB PNG, anything else =

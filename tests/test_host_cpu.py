@@ -270,3 +270,23 @@ def test_raycheck_tool(rtlib, tmp_path):
     m = rtlib.read_image(str(tmp_path / "m.bmp"))
     assert m.shape == (24, 120, 3) and np.array_equal(m[:, 40:80], ref)
     assert raycheck.main([str(tmp_path / "a.png"), str(tmp_path / "b.png"), "--maxrms", "0.0001"]) == 1
+
+
+def test_arena_cache_file(rtlib, scene_dir, tmp_path):
+    """rt_arena_save / rt_arena_load: the cache file is the arena, byte for byte; a truncated,
+    corrupted or foreign file is refused."""
+    arena = rtlib.load_ray_file(str(scene_dir / "trimesh2.ray"))
+    path = tmp_path / "scene.arena"
+    rtlib.save_arena(str(path), arena)
+    back = rtlib.load_arena(str(path))
+    assert back.bytes() == arena.bytes()
+    raw = path.read_bytes()
+    (tmp_path / "short.arena").write_bytes(raw[:-64])
+    (tmp_path / "long.arena").write_bytes(raw + b"\0")
+    bad = bytearray(raw)
+    bad[4] ^= 0xff  # magic / version word
+    (tmp_path / "magic.arena").write_bytes(bytes(bad))
+    (tmp_path / "text.arena").write_bytes(b"SBT-raytracer 1.0\n")
+    for name in ("short.arena", "long.arena", "magic.arena", "text.arena", "missing.arena"):
+        with pytest.raises(rtlib.RtError):
+            rtlib.load_arena(str(tmp_path / name))

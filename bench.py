@@ -393,6 +393,7 @@ def run_b200(args, key, wl, rank, world, local_rank):
                           "partition": "interleaved 32x32 tiles, tile t -> rank t %% %d; scene replicated" % world,
                           "l2": "256 MiB L2 flush between timed frames (its own time subtracted)",
                           "rays": "counted as the instrumented reference counts them; %d shadow rays per frame on this rank are counted but not walked (Phong term exactly 0: their contribution is 0 whatever they hit)" % (culled // max(1, args.steps))},
+               "device_ms_per_step": dev_ms_max / args.steps,  # CUDA events on the launching stream around each frame's device work (max over ranks); the gather is outside them
                "clocks": clocks, "gpu_launches": tot_launches,
                "e2e": {"value": tot_e_rays / e_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": w * h * 3,
                        "what": "rt_upload_scene (whole scene arena, pinned host -> device, layouts rebuilt on the device) + render + RGB8 frame device -> host, every step"}}

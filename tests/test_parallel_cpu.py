@@ -37,12 +37,16 @@ def _worker(rank, world, port, w, h, q):
     dist.destroy_process_group()
 
 
-def test_gather_and_broadcast_world2():
+import pytest
+
+
+@pytest.mark.parametrize("world", [2, 4])  # 4: 35 tiles of the 200x150 frame do not divide evenly, ranks pad
+def test_gather_and_broadcast_world2(world):
     ctx = mp.get_context("spawn")
     for (w, h) in ((200, 150), (64, 32)):
         q = ctx.Queue()
-        port = 29500 + (os.getpid() % 2000)
-        procs = [ctx.Process(target=_worker, args=(r, 2, port, w, h, q)) for r in range(2)]
+        port = 29500 + (os.getpid() % 2000) + world
+        procs = [ctx.Process(target=_worker, args=(r, world, port, w, h, q)) for r in range(world)]
         for p in procs:
             p.start()
         res = [q.get(timeout=120) for _ in procs]

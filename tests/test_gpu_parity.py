@@ -379,3 +379,61 @@ def test_small_wave_width_spills(rtlib, oracle_mod, scene_dir, scene, monkeypatc
             (ref_st.camera_rays, ref_st.reflection_rays, ref_st.refraction_rays, ref_st.shadow_rays)
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("gen,w,h_expect,depth,win", [("dragon", 1920, 1080, 5, 96), ("mixed", 7680, 4320, 8, 64)])
+def test_full_size_configs(rtlib, oracle_mod, tmp_path_factory, gen, w, h_expect, depth, win):
+    """BASELINE.json configs[2] and configs[4] at their FULL sizes (869,556-face dragon stand-in, 1920x1080,
+    depth 5; 1M-primitive mixed scene, 7680x4320, depth 8):
+    - hit ids, t and N of a random sample of primary rays and of their reflections: bit-exact against the
+      unmodified reference (whose classes are filled from the arena: its own load of this scene takes half an hour);
+    - four scattered windows of the frame against the reference's traceImage on the same pixels;
+    - size-independent properties of the whole frame: an 8-way tile partition reassembles to the single-GPU
+      frame bit for bit with the same ray counts, and camera rays = pixels."""
+    import gen_scenes
+    d = tmp_path_factory.mktemp("full")
+    path = d / (gen + ".ray")
+    path.write_text(gen_scenes.GENERATORS[gen](1.0))
+    arena = rtlib.load_ray_file(str(path))
+    orc = oracle_mod.Oracle(None, arena=arena)
+    c = rtlib.Context(0)
+    try:
+        c.upload(arena)
+        h = oracle_mod.frame_height(w, orc.aspect)
+        assert h == h_expect
+        p = rtlib.Params.default(depth=depth)
+        rays = oracle_mod.camera_rays(arena.camera(), w, h)
+        pick = np.random.default_rng(7).choice(len(rays), 30000, replace=False)
+        # centre column and row: rays with a zero direction component (the reference's slab test skips that axis)
+        pick = np.concatenate([pick, np.arange(h) * w + w // 2, (h // 2) * w + np.arange(w)])
+        sub = rays[pick]
+        ref_hits, _ = orc.trace_rays(p, sub, depth, want_rgb=False)
+        dev_hits, _ = c.trace_rays(p, sub, depth, want_rgb=False)
+        assert (ref_hits["obj"] >= 0).sum() > 3000
+        for f in ("obj", "face", "t", "N"):
+            assert np.array_equal(ref_hits[f], dev_hits[f]), f
+        m = ref_hits["obj"] >= 0
+        n, dd = ref_hits["N"][m], sub[m, 3:6]
+        sec = np.zeros((m.sum(), 6))
+        sec[:, 0:3] = sub[m, 0:3] + (ref_hits["t"][m] - 1e-8)[:, None] * dd
+        sec[:, 3:6] = dd + (2 * -(n * dd).sum(axis=1))[:, None] * n
+        ref2, _ = orc.trace_rays(p, sec, depth, want_rgb=False)
+        dev2, _ = c.trace_rays(p, sec, depth, want_rgb=False)
+        for f in ("obj", "face", "t", "N"):
+            assert np.array_equal(ref2[f], dev2[f]), f
+        full, st_full = c.render(p, w, h)
+        assert st_full.camera_rays == w * h
+        for (fx, fy) in ((0.475, 0.455), (0.31, 0.28), (0.625, 0.65), (0.02, 0.055)):
+            i0, j0 = int(fx * w), int(fy * h)
+            ref_win, _, _ = orc.render_window(p, w, h, i0, i0 + win, j0, j0 + win)
+            dwin = oracle_mod.image_diff(ref_win, full[j0:j0 + win, i0:i0 + win])
+            assert dwin["within1"] >= TOL_WITHIN1, ((i0, j0), dwin)
+        out = np.zeros((h, w, 3), np.uint8)
+        counts = np.zeros(4, np.int64)
+        for part in range(8):
+            _, st = c.render(p, w, h, part, 8, out=out)
+            counts += np.array([st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays], dtype=np.int64)
+        assert np.array_equal(out, full)
+        assert tuple(counts) == (st_full.camera_rays, st_full.reflection_rays, st_full.refraction_rays, st_full.shadow_rays)
+    finally:
+        c.close()

@@ -69,7 +69,8 @@ struct WaveCounters {
 	unsigned long long n_children;
 	unsigned long long n_heavy;      // rays of this round that exhausted the node budget
 	unsigned long long heavy_cursor; // next heavy ray to be taken by a warp
-	unsigned long long pad;
+	unsigned long long n_retry;      // rays that exhausted the FIRST budget (k_wave_closest); k_wave_closest_retry walks them
+	                                 // again with a larger one and only its leftovers (n_heavy) go to the cooperative kernel
 	unsigned long long n_shadow[2];  // per round parity: the shadow rays of round r are still being
 	                                 // walked (second stream) while round r+1 fills the other queue
 };
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 #define RT_CLOSEST_MINB 12 // 80 registers: the walk is latency bound, more resident warps beat fewer spills (profiles/r1_variants.txt)
 #endif
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
-                                                                                    int budget, int* heavy, WaveCounters* cnt)
+                                                                                    int budget, int* retry, unsigned long long* n_retry)
 {
 	const long long k = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
 	if (k >= m) return;
@@ -143,11 +144,47 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_clos
 	unused.n = 0;
 	unused.cut = RT_T_INF;
 	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, budget)) {
-		heavy[atomicAdd(&cnt->n_heavy, 1ull)] = (int)k; // k_wave_closest_heavy redoes this ray
+		retry[atomicAdd(n_retry, 1ull)] = (int)k; // k_wave_closest_retry (or, with a forced budget, the cooperative kernel) redoes this ray
 		return;
 	}
 	H.t[k] = C.have ? C.best_t : -1.0;
 	H.of[k] = make_int2(C.best_obj, C.best_fpos);
+}
+
+#define RT_RETRY_MIN 16384 // about 14 rays for each of the cooperative kernel's warps
+// Second chance for the rays that ran out of the first budget: the same single-thread walk with a much
+// larger budget, over the (short) retry list with a fixed grid.  The cooperative kernel keeps one ray per
+// WARP busy and is meant for the few rays that fan out over thousands of nodes; if the first budget was
+// simply too small for the scene (it adapts, but a round may be walked before it has) the retry list can
+// hold a percent of a round - half a million rays - and those are ordinary rays.
+__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest_retry(const __grid_constant__ DScene S, const RayQueue Q, long long base, const HitQueue H,
+                                                                                          int budget, const int* retry, int* heavy, WaveCounters* cnt)
+{
+	const long long n = (long long)cnt->n_retry;
+	// a short list is what the cooperative kernel is for (and a single thread would need a millisecond for a
+	// ray that really fans out): hand it over unchanged
+	const bool forward = n < RT_RETRY_MIN;
+	for (long long j = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x; j < n; j += (long long)gridDim.x * RT_TRACE_THREADS) {
+		const int k = retry[j];
+		if (forward) { heavy[atomicAdd(&cnt->n_heavy, 1ull)] = k; continue; }
+		const long long q = base + k;
+		const d3 ro = Q.load_v(0, q), rd = Q.load_v(3, q);
+		TravClosest C;
+		C.have = false;
+		C.best_t = RT_T_INF;
+		C.best_rank = 0x7fffffff;
+		C.best_obj = -1;
+		C.best_fpos = -1;
+		SBuf unused;
+		unused.n = 0;
+		unused.cut = RT_T_INF;
+		if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, budget)) {
+			heavy[atomicAdd(&cnt->n_heavy, 1ull)] = k; // k_wave_closest_heavy redoes this ray
+			continue;
+		}
+		H.t[k] = C.have ? C.best_t : -1.0;
+		H.of[k] = make_int2(C.best_obj, C.best_fpos);
+	}
 }
 
 // The rays that ran out of budget, one per warp (rt_coop.cuh); persistent grid, dynamic fetch.

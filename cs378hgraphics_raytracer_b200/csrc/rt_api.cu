@@ -34,7 +34,8 @@ struct rt_ctx {
 	size_t buf_bytes[48] = {0};
 	unsigned long long launches = 0;
 	// wavefront path
-	long long wave_width = 1 << 21;        // rays per round (RT_B200_WAVE overrides)
+	long long wave_width = 0;              // rays per round; 0 = chosen per call from the memory budget below (RT_B200_WAVE overrides)
+	size_t queue_budget = 0;               // bytes the ray queues of a round may take: a quarter of the device memory
 	int walk_budget = 96;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
 	int n_area_lights = 0;                 // area + spot lights of the uploaded scene
 	bool budget_auto = true;               // no RT_B200_BUDGET given: the budget adapts to the scene
@@ -57,7 +58,7 @@ struct rt_ctx {
 namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
-       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_SQ2_D, B_SQ2_I,
+       B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
        B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_COUNT };
 static_assert(B_COUNT <= 48, "rt_ctx::buf too small");
 
@@ -154,7 +155,19 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if (A.n_slots <= 0) return RT_OK;
 	// shadow rays one hit can make: one per point / directional light, softShadowRes per area or spot light
 	const int L = (ctx->S.n_lights - ctx->n_area_lights) + ctx->n_area_lights * (A.prm.soft_shadow_res > 0 ? A.prm.soft_shadow_res : 0);
+	// Rays per round.  Wide rounds are faster (fewer launches and tails, fuller late rounds: C5 335 -> 370
+	// Mrays/s from 2 Mi to 32 Mi rays, profiles/r1_variants.txt); the queues cost about 4 * 104 + 2 * L * 80 + 24
+	// bytes per ray of the round, so the width is what a quarter of the device memory holds, at most 32 Mi.
 	long long W = ctx->wave_width;
+	if (W <= 0) {
+		const size_t per_ray = 4 * 104 + 2 * (size_t)(L > 0 ? L : 1) * 80 + 24;
+		W = (long long)(ctx->queue_budget / per_ray) / 1024 * 1024;
+		// the spill stack (allocated only if a round ever has more than W children) may take another half of the memory
+		const long long spill_fit = (long long)(2 * ctx->queue_budget / (((size_t)(A.depth < 30 ? A.depth : 30) + 2) * 104)) / 1024 * 1024;
+		if (W > spill_fit) W = spill_fit;
+		if (W > (32ll << 20)) W = 32ll << 20;
+		if (W < (1ll << 20)) W = 1ll << 20;
+	}
 	const long long fit = ((A.n_slots + 1023) / 1024) * 1024;
 	if (W > fit) W = fit;
 	rt_status st;
@@ -172,6 +185,8 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if ((st = ensure(ctx, B_WH_OF, (size_t)W * sizeof(int2))) != RT_OK) return st;
 	if ((st = ensure(ctx, B_HEAVY, (size_t)W * sizeof(int))) != RT_OK) return st;
 	int* heavy = (int*)ctx->buf[B_HEAVY];
+	if ((st = ensure(ctx, B_RETRY, (size_t)W * sizeof(int))) != RT_OK) return st;
+	int* retry = (int*)ctx->buf[B_RETRY];
 	HitQueue H;
 	H.t = (double*)ctx->buf[B_WH_T];
 	H.of = (int2*)ctx->buf[B_WH_OF];
@@ -212,7 +227,15 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		if (m == 0) break;
 		const int par = (int)(round & 1);
 		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
-		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget, heavy, cnt));
+		// a forced budget (RT_B200_BUDGET, the tests) sends its leftovers straight to the cooperative kernel
+		const bool second = ctx->budget_auto && ctx->walk_budget > 0;
+		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget,
+		                                                                                                                second ? retry : heavy, second ? &cnt->n_retry : &cnt->n_heavy));
+		if (second) {
+			// second chance with 8 x the budget: grid for 1/32 of the round (a grid-stride loop takes whatever there is)
+			const unsigned rblocks = blocks_for((m + 31) / 32, RT_TRACE_THREADS);
+			STAGE(RT_STAGE_COOP, k_wave_closest_retry<<<rblocks < 8u ? 8u : rblocks, RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, H, ctx->walk_budget * 8, retry, heavy, cnt));
+		}
 		if (ctx->walk_budget > 0)
 			STAGE(RT_STAGE_COOP, k_wave_closest_heavy<<<ctx->sm_count * 4 * (2 / RT_COOP_WARPS), 32 * RT_COOP_WARPS, 0, ctx->stream>>>(ctx->S, cur, base, H, heavy, cnt));
 		// this parity's shadow queue is free once the shadow kernel of two rounds ago is done; only the
@@ -221,7 +244,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		shadow_pending[par] = false;
 		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
-		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		if (L > 0) {
 			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
@@ -240,7 +263,9 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		// the node budget follows the scene: if more than ~1.5 % of a round's rays ran out of it, the
 		// ordinary walk of this scene is simply longer (deep scene-level trees) - double it.  Either
 		// path gives the same hit, so this only moves work between the two kernels.
-		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)ctx->pinned[1] * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
+		// (pinned[3]: the rays that ran out of the first budget.  A round walked before the budget has grown is not
+		// lost: its leftovers get a second single-thread chance, k_wave_closest_retry.)
+		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)ctx->pinned[3] * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
 		round++;
 		const RayQueue tmp = cur;
 		cur = nxt;
@@ -319,6 +344,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	cudaDeviceProp prop;
 	if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return RT_ERR_NO_DEVICE; }
 	ctx->sm_count = prop.multiProcessorCount;
+	ctx->queue_budget = prop.totalGlobalMem / 4;
 	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	cudaEventCreate(&ctx->ev0);
 	cudaEventCreate(&ctx->ev1);

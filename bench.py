@@ -413,8 +413,14 @@ def run_b200(args, key, wl, rank, world, local_rank):
             n_rays = kind_rays[0 if kind == "closest" else 1]
             alg_bytes = ck["bytes_per_ray"] * n_rays
             ach = alg_bytes / (k_ms * 1e-3) / 1e9
+            # DRAM bytes of this kernel's average launch, from the committed ncu capture of one launch scaled by duration
+            tr = load_dram_traffic(key, kind)
+            traffic, traffic_src = None, None
+            if isinstance(tr, dict) and tr.get("launch_ms"):
+                traffic = tr["bytes"] * (k_ms / max(k_n, 1)) / tr["launch_ms"]
+                traffic_src = "%s; scaled from its %.2f ms to this run's %.2f ms per launch" % (tr.get("source", ""), tr["launch_ms"], k_ms / max(k_n, 1))
             out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                               "traffic": load_dram_traffic(key, kind), "peak_source": peak_src, "kernel": kernel,
+                               "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": kernel,
                                "kernel_ms_per_launch": k_ms / max(k_n, 1), "launches_per_step": k_n / args.steps,
                                "algorithmic_bytes_per_launch": alg_bytes / max(k_n, 1), "bytes_per_ray": ck["bytes_per_ray"],
                                "note": "the walk is FP64-latency bound, not bandwidth bound: the scene is L2 resident (DESIGN.md, roofline)",

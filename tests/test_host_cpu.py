@@ -290,3 +290,22 @@ def test_arena_cache_file(rtlib, scene_dir, tmp_path):
     for name in ("short.arena", "long.arena", "magic.arena", "text.arena", "missing.arena"):
         with pytest.raises(rtlib.RtError):
             rtlib.load_arena(str(tmp_path / name))
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py --impl reference (the reference's own CPU path through oracle/_ref) runs without a GPU and
+    prints exactly one JSON line with the keys the measurement contract names."""
+    import json
+    import sys
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref_oracle.so")):
+        pytest.skip("oracle/_ref not built")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "c1", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "Mrays/s" and d["higher_is_better"] is True and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "workload" in d["config"] and d["metric"].startswith("Mrays/s")

@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 
 // ---- stage 3: Light::shadowAttenuation ------------------------------------------------------------
 #ifndef RT_SHADOW_MINB
-#define RT_SHADOW_MINB 12 // 80 registers (re-swept after the walk changed: profiles/r1_variants.txt)
+#define RT_SHADOW_MINB 16 // 64 registers, 16 blocks per SM (re-swept with wide rounds: profiles/r1_variants.txt)
 #endif
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt)
 {

@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 
 // ---- stage 1: Scene::intersect ----------------------------------------------------------------
 #ifndef RT_CLOSEST_MINB
-#define RT_CLOSEST_MINB 12 // 80 registers: the walk is latency bound, more resident warps beat fewer spills (profiles/r1_variants.txt)
+#define RT_CLOSEST_MINB 14 // 72 registers: the walk is latency bound, more resident warps beat fewer spills (profiles/r1_variants.txt)
 #endif
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
                                                                                     int budget, int* retry, unsigned long long* n_retry)

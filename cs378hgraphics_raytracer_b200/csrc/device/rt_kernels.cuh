@@ -165,6 +165,9 @@ __global__ void __launch_bounds__(256) k_adapt_init(const PoolArgs A, long long 
 	regions[pix] = r;
 }
 
+// valid(region) is adaptaa's first line (RayTracer.cpp:319)
+__device__ __forceinline__ bool region_valid(const Region& r) { return !(r.x1 + 0.0001 >= r.x2 || r.y1 + 0.0001 >= r.y2); }
+
 // sample coordinates of every region of one level
 __global__ void __launch_bounds__(256) k_adapt_samples(const Region* regions, long long n_regions, int N, double* xs, double* ys)
 {
@@ -173,13 +176,14 @@ __global__ void __launch_bounds__(256) k_adapt_samples(const Region* regions, lo
 	const Region r = regions[t / N];
 	const int k = (int)(t % N);
 	const double w = r.x2 - r.x1, h = r.y2 - r.y1;
-	xs[t] = radical_inverse2(k) * w + r.x1;
+	// adaptaa returns before it samples a region that fails its size test (RayTracer.cpp:319) - the padding pixels of
+	// edge tiles, or pixels narrower than 1e-4 of the window: no rays, and none counted (NaN = k_wave_gen skips the slot)
+	xs[t] = region_valid(r) ? radical_inverse2(k) * w + r.x1 : NAN;
 	ys[t] = 0.0 * h + r.y1;
 }
 
 // mean / deviation test of each region; either adds its mean (scaled by 4^-level) to the pixel or
-// emits its four quadrants for the next level.  valid(region) is adaptaa's first line (:319).
-__device__ __forceinline__ bool region_valid(const Region& r) { return !(r.x1 + 0.0001 >= r.x2 || r.y1 + 0.0001 >= r.y2); }
+// emits its four quadrants for the next level.
 
 __global__ void __launch_bounds__(256) k_adapt_resolve(const Region* regions, long long n_regions, int N, const double* accum, rt_params prm,
                                                       double* pix_accum, Region* next, unsigned long long* next_count, unsigned long long next_cap)

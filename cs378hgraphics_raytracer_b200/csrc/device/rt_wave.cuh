@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 		} else {
 			x = A.xs[smp];
 			y = A.ys[smp];
+			ok = x == x; // NaN: a sample of a region adaptaa does not sample (k_adapt_samples)
 		}
 		if (ok) primary_ray(S.cam, A.prm, x, y, lens, A.eye_shift, ro, rd);
 	}

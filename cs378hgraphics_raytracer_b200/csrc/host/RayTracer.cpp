@@ -76,8 +76,9 @@ dvec3 RayTracer::tracePixel(int i, int j)
 	const int32_t ij[2] = {i, j};
 	double rgb[3] = {0, 0, 0};
 	if (rt_trace_pixels(ctx, &ui, buffer_width, buffer_height, ij, 1, rgb) != RT_OK) { alert(rt_last_error(ctx)); return col; }
+	// like the reference (RayTracer.cpp:81-102) tracePixel only RETURNS the colour: in supersampling mode (i, j)
+	// are sub-pixel coordinates in [0, w*s) x [0, h*s), which do not index the buffer; traceImage stores pixels
 	col = {rgb[0], rgb[1], rgb[2]};
-	setPixel(i, j, col); // tracePixel writes the pixel it traced (RayTracer.cpp:100)
 	return col;
 }
 
@@ -86,7 +87,9 @@ dvec3 RayTracer::traceRay(ray& r, double thresh, int depth, double& length, dvec
 	dvec3 col = {0, 0, 0};
 	if (!loaded) return col;
 	rt_params p = ui;
-	p.aterm_thresh = thresh;
+	// `thresh` takes effect only while traceUI->aTermSwitch() is set (RayTracer.cpp:125, light.cpp:48); in rt_params the
+	// switch is "aterm_thresh > 0", so a caller passing getATermThresh() with the switch off gets no adaptive termination
+	p.aterm_thresh = (ui.aterm_thresh > 0.0) ? thresh : 0.0;
 	rt_ray rr = {{r.p.x, r.p.y, r.p.z}, {r.d.x, r.d.y, r.d.z}};
 	rt_hit hit;
 	double rgb[3];

@@ -73,7 +73,9 @@ static bool tree_ok(const rt_node* n, uint64_t n_nodes, uint64_t n_items, uint64
 		if (n[k].right >= 0) {
 			if ((uint64_t)n[k].right >= n_nodes || (uint64_t)n[k].right <= k + 1) return false;
 		} else {
-			if (n[k].first < 0 || n[k].count < 0 || (uint64_t)n[k].first + n[k].count > n_items) return false;
+			// count <= 3 (kdTree.h LEAF_NUM) and first < 2^29: leaf_ref packs (first << 2 | count) into 31 bits and the
+			// walks keep a 3-bit pending mask per leaf - the same limits the device check applies (k_derive_nodes2)
+			if (n[k].first < 0 || n[k].count < 0 || n[k].count > 3 || n[k].first >= (1 << 29) || (uint64_t)n[k].first + n[k].count > n_items) return false;
 			for (int32_t i = 0; i < n[k].count; i++)
 				if (items[n[k].first + i] < 0 || (uint64_t)items[n[k].first + i] >= item_limit) return false;
 		}

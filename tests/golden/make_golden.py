@@ -21,14 +21,31 @@ sys.path.insert(0, os.path.join(ROOT, "scenes"))
 W = 64
 DEPTH = 5
 SCENES = {"hitchcock": ("gen", "hitchcock", 1.0), "trimesh2": ("gen", "trimesh2", 1.0), "dragon_small": ("gen", "dragon", 0.02),
-          "prims_mixed": ("file", "prims_mixed.ray"), "lights_area": ("file", "lights_area.ray")}
+          "prims_mixed": ("file", "prims_mixed.ray"), "lights_area": ("file", "lights_area.ray"), "tex_params": ("tex",),
+          # the reference's own fixtures (ray/newScene, copied by tests/fetch_ref_fixtures.py)
+          "ref_box_cyl_opaque_shadow_spotlight": ("ref", "box_cyl_opaque_shadow_spotlight.ray"), "ref_concrete_1": ("ref", "concrete_1.ray"),
+          "ref_concrete_2": ("ref", "concrete_2.ray"), "ref_concrete_3": ("ref", "concrete_3.ray"), "ref_distance": ("ref", "distance.ray"),
+          "ref_lava_box": ("ref", "lava_box.ray"), "ref_spheres_overlap": ("ref", "spheres_overlap.ray")}
 
 
-def scene_text(spec):
+def scene_file(spec, d, name):
+    """Path of the scene's .ray file (written into d unless it is one of the reference's fixtures)."""
     import gen_scenes
+    if spec[0] == "ref":
+        import fetch_ref_fixtures
+        return os.path.join(fetch_ref_fixtures.fetch(), spec[1])
     if spec[0] == "gen":
-        return gen_scenes.GENERATORS[spec[1]](spec[2])
-    return open(os.path.join(ROOT, "tests", "scenes", spec[1])).read()
+        text = gen_scenes.GENERATORS[spec[1]](spec[2])
+    elif spec[0] == "tex":
+        import conftest
+        gen_scenes.gen_cubemap(os.path.join(d, "cubemap"), 64)
+        text = conftest.tex_params_scene(d)
+    else:
+        text = open(os.path.join(ROOT, "tests", "scenes", spec[1])).read()
+    path = os.path.join(d, name + ".ray")
+    with open(path, "w") as f:
+        f.write(text)
+    return path
 
 
 def main():
@@ -36,10 +53,11 @@ def main():
     import oracle_binding as ob
     out_dir = os.path.dirname(os.path.abspath(__file__))
     with tempfile.TemporaryDirectory() as d:
+        only = sys.argv[1:]
         for name, spec in SCENES.items():
-            path = os.path.join(d, name + ".ray")
-            with open(path, "w") as f:
-                f.write(scene_text(spec))
+            if only and name not in only:
+                continue
+            path = scene_file(spec, d, name)
             arena = rt.load_ray_file(path)
             orc = ob.Oracle(path)
             h = ob.frame_height(W, orc.aspect)

@@ -11,7 +11,11 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-SCENES = ["hitchcock.ray", "trimesh2.ray", "dragon_small.ray", "mixed_small.ray", "prims_mixed.ray", "lights_area.ray"]
+from conftest import GOLDEN, REF_SCENES
+
+# generated stand-ins, hand-written scenes, every texture-mapped material parameter (conftest.tex_params_scene) and the
+# reference's own fixtures ray/newScene/*.ray with their BMP texture / bump maps ("ref:", tests/fetch_ref_fixtures.py)
+SCENES = ["hitchcock.ray", "trimesh2.ray", "dragon_small.ray", "mixed_small.ray", "prims_mixed.ray", "lights_area.ray", "tex_params.ray"] + REF_SCENES
 W = 320
 TOL_WITHIN1 = 0.999
 
@@ -31,8 +35,8 @@ def _load(rtlib, oracle_mod, ctx, path, cubemap=None):
 
 
 @pytest.mark.parametrize("scene", SCENES)
-def test_primary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_dir, scene):
-    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+def test_primary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_path, scene):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_path(scene))
     h = oracle_mod.frame_height(W, orc.aspect)
     rays = oracle_mod.camera_rays(arena.camera(), W, h)
     p = rtlib.Params.default(depth=5)
@@ -46,9 +50,9 @@ def test_primary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_dir, scene):
 
 
 @pytest.mark.parametrize("scene", SCENES)
-def test_secondary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_dir, scene):
+def test_secondary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_path, scene):
     """Rays that start ON surfaces (the self-intersection epsilons): reflect every primary hit."""
-    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_path(scene))
     h = oracle_mod.frame_height(160, orc.aspect)
     rays = oracle_mod.camera_rays(arena.camera(), 160, h)
     p = rtlib.Params.default(depth=5)
@@ -66,10 +70,10 @@ def test_secondary_hits_bit_exact(rtlib, oracle_mod, ctx, scene_dir, scene):
 
 
 @pytest.mark.parametrize("scene", SCENES)
-def test_trace_ray_colours(rtlib, oracle_mod, ctx, scene_dir, scene):
+def test_trace_ray_colours(rtlib, oracle_mod, ctx, scene_path, scene):
     """RayTracer::traceRay colours (unclamped doubles): only libm pow/sin/cos and the summation
     order differ between host and device, so 1e-9 absolute is generous."""
-    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_path(scene))
     h = oracle_mod.frame_height(128, orc.aspect)
     rays = oracle_mod.camera_rays(arena.camera(), 128, h)
     p = rtlib.Params.default(depth=5)
@@ -79,8 +83,8 @@ def test_trace_ray_colours(rtlib, oracle_mod, ctx, scene_dir, scene):
 
 
 @pytest.mark.parametrize("scene", SCENES)
-def test_frame_and_ray_counts(rtlib, oracle_mod, ctx, scene_dir, scene):
-    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / scene)
+def test_frame_and_ray_counts(rtlib, oracle_mod, ctx, scene_path, scene):
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_path(scene))
     h = oracle_mod.frame_height(W, orc.aspect)
     p = rtlib.Params.default(depth=5)
     ref_img, ref_st, _ = orc.render(p, W, h)
@@ -132,8 +136,26 @@ def test_adaptive_aa_with_cubemap(rtlib, oracle_mod, ctx, scene_dir, cubemap_fac
         ref_img, ref_st, _ = orc.render(p, 128, 128)
         dev_img, dev_st = ctx.render(p, 128, 128)
         d = oracle_mod.image_diff(ref_img, dev_img)
-        assert d["within1"] >= 0.995, d  # the subdivision decision itself is a float threshold
-        assert abs(int(dev_st.camera_rays) - int(ref_st.camera_rays)) <= 0.02 * ref_st.camera_rays
+        # the north star's bar.  The subdivision decision is a comparison of a deviation (differing from the reference's
+        # by ~1e-16: libm pow, summation order) with the threshold, so a flipped decision needs a region within
+        # 1e-15 of the threshold: the sample counts agree too
+        assert d["within1"] >= TOL_WITHIN1, (thresh, d)
+        assert abs(int(dev_st.camera_rays) - int(ref_st.camera_rays)) <= 1e-3 * ref_st.camera_rays, (thresh, dev_st.camera_rays, ref_st.camera_rays)
+
+
+@pytest.mark.parametrize("w,h", [(100, 75), (33, 65)])
+def test_adaptive_aa_edge_tiles_count_no_phantom_samples(rtlib, oracle_mod, ctx, scene_dir, w, h):
+    """Frame sizes that are not multiples of the 32x32 tile: the padding pixels of edge tiles are regions adaptaa
+    never samples (RayTracer.cpp:319 size test) - no rays may be traced or counted for them."""
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_dir / "prims_mixed.ray")
+    p = rtlib.Params.default(depth=4, aa_mode=2, aa_samples=3, aa_thresh=0.05)
+    ref_img, ref_st, _ = orc.render(p, w, h)
+    dev_img, dev_st = ctx.render(p, w, h)
+    d = oracle_mod.image_diff(ref_img, dev_img)
+    assert d["within1"] >= TOL_WITHIN1, d
+    for f in ("camera_rays", "reflection_rays", "refraction_rays", "shadow_rays"):
+        a, b = int(getattr(ref_st, f)), int(getattr(dev_st, f))
+        assert abs(a - b) <= max(2, 1e-3 * a), (f, a, b)
 
 
 def test_cubemap_and_supersample(rtlib, oracle_mod, ctx, scene_dir, cubemap_faces):
@@ -270,11 +292,11 @@ def test_zero_term_shadow_rays_are_counted_not_walked(rtlib, oracle_mod, scene_d
 
 
 @pytest.mark.parametrize("scene", SCENES)
-def test_device_built_layouts_match_host(rtlib, ctx, scene_dir, scene):
+def test_device_built_layouts_match_host(rtlib, ctx, scene_path, scene):
     """rt_upload_scene builds the wide nodes / triangle records / tree descriptors with device
     kernels; the host construction (rt_derive.hpp, the one tests/hostsim walks) must agree byte
     for byte."""
-    arena = rtlib.load_ray_file(str(scene_dir / scene))
+    arena = rtlib.load_ray_file(str(scene_path(scene)))
     ctx.upload(arena)
     assert ctx.selftest_derive(arena) == 0
 
@@ -328,18 +350,14 @@ def test_cli_renders_reference_frame(rtlib, oracle_mod, scene_dir, tmp_path):
     assert np.array_equal(rtlib.read_image(str(out_png)), px)
 
 
-GOLDEN = {"hitchcock": "hitchcock.ray", "trimesh2": "trimesh2.ray", "dragon_small": "dragon_small.ray", "prims_mixed": "prims_mixed.ray",
-          "lights_area": "lights_area.ray"}
-
-
 @pytest.mark.parametrize("name", sorted(GOLDEN))
-def test_golden_vectors(rtlib, ctx, scene_dir, name):
+def test_golden_vectors(rtlib, ctx, scene_path, name):
     """Committed outputs of the unmodified reference (tests/golden/make_golden.py): hit records of
     every camera ray bit-exact, traceRay colours, the RGB8 frame and the ray counters.  Needs no
     oracle library on the box."""
     import os
     g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
-    arena = rtlib.load_ray_file(str(scene_dir / GOLDEN[name]))
+    arena = rtlib.load_ray_file(str(scene_path(GOLDEN[name])))
     ctx.upload(arena)
     w, h, depth = int(g["w"]), int(g["h"]), int(g["depth"])
     p = rtlib.Params.default(depth=depth)

@@ -18,7 +18,11 @@ import numpy as np
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SMALL = ["hitchcock.ray", "trimesh2.ray", "prims_mixed.ray", "dragon_small.ray", "mixed_small.ray", "lights_area.ray"]
+from conftest import REF_SCENES
+
+# generated stand-ins, hand-written scenes (tests/scenes), every texture-mapped parameter (conftest.tex_params_scene)
+# and the reference's own seven fixtures ray/newScene/*.ray with their BMP texture and bump maps ("ref:")
+SMALL = ["hitchcock.ray", "trimesh2.ray", "prims_mixed.ray", "dragon_small.ray", "mixed_small.ray", "lights_area.ray", "tex_params.ray"] + REF_SCENES
 
 
 # ---------------------------------------------------------------------------------------------
@@ -80,10 +84,10 @@ def test_arena_validate_rejects_damage(rtlib, scene_dir):
 
 # ---------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("scene", SMALL)
-def test_arena_matches_reference_flatten(rtlib, oracle_mod, scene_dir, scene):
+def test_arena_matches_reference_flatten(rtlib, oracle_mod, scene_path, scene):
     """rt_load_ray_file == what the reference's parser + Scene::conclude + Trimesh::conclude +
     KdTree build leave in memory, flattened by the harness: byte for byte."""
-    path = scene_dir / scene
+    path = scene_path(scene)
     mine = rtlib.load_ray_file(str(path)).bytes()
     orc = oracle_mod.Oracle(str(path))
     theirs = orc.flatten()
@@ -112,11 +116,11 @@ def hostsim():
 
 @pytest.mark.parametrize("scene", SMALL)
 @pytest.mark.parametrize("prune", [0, 1])
-def test_device_code_on_host_hits_bit_exact(rtlib, oracle_mod, hostsim, scene_dir, scene, prune):
+def test_device_code_on_host_hits_bit_exact(rtlib, oracle_mod, hostsim, scene_path, scene, prune):
     """prune=0 is the reference's exhaustive walk, prune=1 the front-to-back walk with culling:
     both must name the reference's winner, with the same t and normal, bit for bit."""
     from cs378hgraphics_raytracer_b200.binding import HIT_DTYPE
-    path = scene_dir / scene
+    path = scene_path(scene)
     arena = rtlib.load_ray_file(str(path))
     orc = oracle_mod.Oracle(str(path))
     w = 96
@@ -134,9 +138,9 @@ def test_device_code_on_host_hits_bit_exact(rtlib, oracle_mod, hostsim, scene_di
     assert np.abs(ref_rgb - rgb).max() < 1e-9
 
 
-@pytest.mark.parametrize("scene", ["hitchcock.ray", "prims_mixed.ray", "dragon_small.ray", "lights_area.ray"])
-def test_device_code_on_host_frame_and_ray_counts(rtlib, oracle_mod, hostsim, scene_dir, scene):
-    path = scene_dir / scene
+@pytest.mark.parametrize("scene", ["hitchcock.ray", "prims_mixed.ray", "dragon_small.ray", "lights_area.ray", "tex_params.ray"] + REF_SCENES)
+def test_device_code_on_host_frame_and_ray_counts(rtlib, oracle_mod, hostsim, scene_path, scene):
+    path = scene_path(scene)
     arena = rtlib.load_ray_file(str(path))
     orc = oracle_mod.Oracle(str(path))
     w = 80
@@ -192,17 +196,16 @@ def test_cli_fails_loudly_without_gpu(scene_dir, tmp_path):
     assert not (tmp_path / "o.bmp").exists()
 
 
-GOLDEN = {"hitchcock": "hitchcock.ray", "trimesh2": "trimesh2.ray", "dragon_small": "dragon_small.ray", "prims_mixed": "prims_mixed.ray",
-          "lights_area": "lights_area.ray"}
+from conftest import GOLDEN
 
 
 @pytest.mark.parametrize("name", sorted(GOLDEN))
-def test_golden_vectors_hostsim(rtlib, hostsim, scene_dir, name):
+def test_golden_vectors_hostsim(rtlib, hostsim, scene_path, name):
     """The committed reference outputs (tests/golden) against the host build of the device code:
     runs without the oracle library."""
     from cs378hgraphics_raytracer_b200.binding import HIT_DTYPE
     g = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
-    arena = rtlib.load_ray_file(str(scene_dir / GOLDEN[name]))
+    arena = rtlib.load_ray_file(str(scene_path(GOLDEN[name])))
     w, h, depth = int(g["w"]), int(g["h"]), int(g["depth"])
     p = rtlib.Params.default(depth=depth)
     rays = np.ascontiguousarray(g["rays"])

@@ -140,6 +140,7 @@ inline void derive(const rt::ArenaView& A, Derived& D)
 		if (obj < 0 || (uint64_t)obj >= A.count(RT_SEC_OBJECTS)) continue;
 		for (int c = 0; c < 3; c++) { b.lo[c] = (float)objs[obj].bbox[c]; b.hi[c] = (float)objs[obj].bbox[3 + c]; }
 		b.obj = obj;
+		b.type = objs[obj].type;
 	}
 }
 

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) k_derive_itembox(const int32_t* sitems, l
 		b.hi[c] = ok ? (float)objs[obj].bbox[3 + c] : 0.0f;
 	}
 	b.obj = ok ? obj : 0;
-	b.pad = 0;
+	b.type = ok ? objs[obj].type : 0;
 	out[k] = b;
 }
 

@@ -100,34 +100,60 @@ struct RayInv {
 	// width of the exponent window of `a` served by div_by's FMA path
 	RT_HD unsigned span() const { return fma_ok() ? 1201u : 0u; }
 };
-// Single-precision image of the ray for the box PRE-test (rt_prims.cuh: box2_hit).  With node boxes
-// rounded to float, every slab quotient computed in float differs from the reference's double
-// quotient by less than  4u|q| + 1.1u (E + |o_i|) |y_i|  (u = 2^-24, E = largest |coordinate| of the
-// tree's root box).  amax carries the absolute part with a 3.6x margin; it is +inf when a direction
-// component is zero or anything is out of float range, which makes every box "ambiguous" and hands
-// the decision to the double-precision test.
+// Single-precision image of the ray for the box PRE-test (rt_prims.cuh: boxf).  A slab quotient is
+// computed as ONE fused multiply-add  q~ = RN32(b~ * y~ + p~)  with b~ = RN32(box coordinate),
+// y~ = RN32(1/d_i), p~ = RN32(-(o_i * (1/d_i))) (product in double, rounded once).  With u = 2^-24:
+//     q~ - (b - o_i)/d_i  =  y (b (e_b + e_y) - o_i e_p) + e_q q~,   |e_*| <= u (1 + 2^-20)
+// so |q~ - q| < 2u (E + |o_i|) |y_i| + u |q|  (E = largest |coordinate| of the tree's root box; the
+// reference's own double rounding, 2^-53 relative, is far below this).  amax carries the absolute part
+// with a 3x margin (6u max_i (E + |o_i|)|y_i|); the relative part is covered by the 2^-20 (|tn| + |tf|)
+// term of the test (16x).  amax is +inf when a direction component is zero or anything is out of float
+// range, which makes every box "ambiguous" and hands the decision to the double-precision test.
 RT_HD void make_inv(RayInv& I, const d3& d, double slack);
 struct RayF {
-	float ox, oy, oz;
-	float yx, yy, yz;
+	float yx, yy, yz; // RN32(1/d)
+	float px, py, pz; // RN32(-(o * (1/d)))
 	float amax;
+	float slf;        // RayInv::slmax rounded up: the pruning slack of the float entry distances
 };
-RT_HD bool div_range_ok(double d) { const double a = fabs(d); return d == 0.0 || (a >= 0x1p-300 && a <= 0x1p300); }
-RT_HD void make_rayf(RayF& F, const d3& o, const d3& d, const d3& y, double extent)
+// smallest float >= x / largest float <= x (x finite or +-inf)
+RT_HD float f_up(double x)
 {
-	F.ox = (float)o.x; F.oy = (float)o.y; F.oz = (float)o.z;
+#ifdef __CUDA_ARCH__
+	return __double2float_ru(x);
+#else
+	float f = (float)x;
+	if ((double)f < x) f = nextafterf(f, INFINITY);
+	return f;
+#endif
+}
+RT_HD float f_dn(double x)
+{
+#ifdef __CUDA_ARCH__
+	return __double2float_rd(x);
+#else
+	float f = (float)x;
+	if ((double)f > x) f = nextafterf(f, -INFINITY);
+	return f;
+#endif
+}
+RT_HD bool div_range_ok(double d) { const double a = fabs(d); return d == 0.0 || (a >= 0x1p-300 && a <= 0x1p300); }
+RT_HD void make_rayf(RayF& F, const d3& o, const d3& d, const d3& y, double extent, double slmax)
+{
 	F.yx = (float)y.x; F.yy = (float)y.y; F.yz = (float)y.z;
+	F.px = (float)(-(o.x * y.x)); F.py = (float)(-(o.y * y.y)); F.pz = (float)(-(o.z * y.z));
 	const double ax = (extent + fabs(o.x)) * fabs(y.x), ay = (extent + fabs(o.y)) * fabs(y.y), az = (extent + fabs(o.z)) * fabs(y.z);
 	double m = ax > ay ? ax : ay;
 	m = az > m ? az : m;
 	const bool ok = d.x != 0.0 && d.y != 0.0 && d.z != 0.0 && fabs(y.x) <= 1e15 && fabs(y.y) <= 1e15 && fabs(y.z) <= 1e15 &&
 	                extent + fabs(o.x) <= 1e15 && extent + fabs(o.y) <= 1e15 && extent + fabs(o.z) <= 1e15;
-	F.amax = ok ? (float)(m * 0x1p-22) * 1.0001f + 1e-30f : INFINITY; // m 2^-22 = 4u m, rounded up
+	F.amax = ok ? (float)(m * 0x1.8p-22) * 1.0001f + 1e-30f : INFINITY; // 6u m, rounded up
+	F.slf = f_up(slmax);
 }
 RT_COLD void make_inv(RayInv& I, RayF& F, const d3& o, const d3& d, double slack, double extent)
 {
 	make_inv(I, d, slack);
-	make_rayf(F, o, d, I.y, extent);
+	make_rayf(F, o, d, I.y, extent, I.slmax);
 }
 RT_HD void make_inv(RayInv& I, const d3& d, double slack)
 {

@@ -100,43 +100,60 @@ RT_NODE_ATTR bool box_hit_node(const double* bmin, const double* bmax, const d3&
 	return box_hit(bmin, bmax, o, d, I, entry);
 }
 
-// Both children of a node at once, float first.  Per child the float test ends in one of three
-// states: certainly hit, certainly missed (by the margins derived at RayF), or ambiguous - and only
-// an ambiguous child reads its double box and takes box_hit.  e0/e1 are conservative entry
-// distances (never above the exact tMin minus the pruning slack).
+// Float slab test of one box against the ray's single-precision image (RayF, rt_math.cuh): 6 FMAs,
+// min / max, and a three-way answer by the margins derived there:
+//   0 = the reference's double test certainly answers "miss"
+//   1 = it certainly answers "hit"; e = a conservative entry distance (never above the exact tMin
+//       minus the pruning slack: tn - s lies below the exact tMin by more than the rounding of the
+//       two float subtractions that follow)
+//   2 = ambiguous (grazing rays, boxes touching the origin, zero direction components, NaN): the
+//       caller runs the double test on the double box
+RT_HD int boxf(const float* lo, const float* hi, const RayF& F, float& e)
+{
+	const float qx1 = fmaf(lo[0], F.yx, F.px), qx2 = fmaf(hi[0], F.yx, F.px);
+	const float qy1 = fmaf(lo[1], F.yy, F.py), qy2 = fmaf(hi[1], F.yy, F.py);
+	const float qz1 = fmaf(lo[2], F.yz, F.pz), qz2 = fmaf(hi[2], F.yz, F.pz);
+	const float tn = fmaxf(fmaxf(fminf(qx1, qx2), fminf(qy1, qy2)), fminf(qz1, qz2));
+	const float tf = fminf(fminf(fmaxf(qx1, qx2), fmaxf(qy1, qy2)), fmaxf(qz1, qz2));
+	const float s = fmaf(0x1p-20f, fabsf(tn) + fabsf(tf), 2.0f * F.amax);
+	const float gap = tf - tn;
+	e = (tn - s) - F.slf;
+	if (gap < -s || tf + s < (float)RT_RAY_EPSILON) return 0;
+	if (gap > s && tf - s > (float)RT_RAY_EPSILON * 1.0001f) return 1;
+	return 2;
+}
+
+// The double-precision decision for an ambiguous box of a tree node, entry distance rounded down to float.
+RT_COLD int boxf_resolve(const double* lo, const double* hi, const d3& o, const d3& d, const RayInv& I, float& e)
+{
+	double ed;
+	const bool h = box_hit_node(lo, hi, o, d, I, ed);
+	e = h ? f_dn(ed) : 0.0f;
+	return h ? 1 : 0;
+}
+
+// Both children of a node with double entry distances (the warp-cooperative walk, rt_coop.cuh).
 RT_HD void box2_hit(const DNode2f& nf, const DNode2& n, const d3& o, const d3& d, const RayInv& I, const RayF& F, bool& h0, bool& h1, double& e0, double& e1)
 {
-#define RT_BOXF(LO, HI, H, E, LO64, HI64)                                                        \
-	{                                                                                            \
-		const float qx1 = (LO[0] - F.ox) * F.yx, qx2 = (HI[0] - F.ox) * F.yx;                    \
-		const float qy1 = (LO[1] - F.oy) * F.yy, qy2 = (HI[1] - F.oy) * F.yy;                    \
-		const float qz1 = (LO[2] - F.oz) * F.yz, qz2 = (HI[2] - F.oz) * F.yz;                    \
-		const float tn = fmaxf(fmaxf(fminf(qx1, qx2), fminf(qy1, qy2)), fminf(qz1, qz2));        \
-		const float tf = fminf(fminf(fmaxf(qx1, qx2), fmaxf(qy1, qy2)), fmaxf(qz1, qz2));        \
-		const float s = 2.0f * F.amax + 0x1p-20f * (fabsf(tn) + fabsf(tf));                      \
-		const float gap = tf - tn;                                                               \
-		if (gap < -s || tf + s < (float)RT_RAY_EPSILON) { H = false; E = 0.0; }                  \
-		else if (gap > s && tf - s > (float)RT_RAY_EPSILON * 1.0001f) { H = true; E = (double)(tn - s) - I.slmax; } \
-		else H = box_hit_node(LO64, HI64, o, d, I, E);                                           \
-	}
-	RT_BOXF(nf.lo0, nf.hi0, h0, e0, n.lo0, n.hi0)
-	RT_BOXF(nf.lo1, nf.hi1, h1, e1, n.lo1, n.hi1)
-#undef RT_BOXF
+	float f0, f1;
+	int r0 = boxf(nf.lo0, nf.hi0, F, f0), r1 = boxf(nf.lo1, nf.hi1, F, f1);
+	if (r0 == 2) r0 = boxf_resolve(n.lo0, n.hi0, o, d, I, f0);
+	if (r1 == 2) r1 = boxf_resolve(n.lo1, n.hi1, o, d, I, f1);
+	h0 = r0 != 0;
+	h1 = r1 != 0;
+	e0 = (double)f0;
+	e1 = (double)f1;
 }
 
 // Object bounding boxes (Geometry::intersect's pre-test, scene.cpp:15): true when the float test
-// proves that the reference's double test answers "miss" (same margins as box2_hit); anything
-// else - hit, ambiguous, zero direction components (amax = inf), NaN - is false and the caller runs
-// the double test on the object's own box.
-RT_HD bool box_miss_f(const DItemBox& b, const RayF& F)
+// proves that the reference's double test answers "miss", or - pruned walks - that the box is entered
+// beyond `limf` (a float >= the walk's limit); anything else - hit, ambiguous, zero direction
+// components (amax = inf), NaN - is false and the caller runs the double test on the object's own box.
+RT_HD bool box_miss_f(const DItemBox& b, const RayF& F, float limf = INFINITY)
 {
-	const float qx1 = (b.lo[0] - F.ox) * F.yx, qx2 = (b.hi[0] - F.ox) * F.yx;
-	const float qy1 = (b.lo[1] - F.oy) * F.yy, qy2 = (b.hi[1] - F.oy) * F.yy;
-	const float qz1 = (b.lo[2] - F.oz) * F.yz, qz2 = (b.hi[2] - F.oz) * F.yz;
-	const float tn = fmaxf(fmaxf(fminf(qx1, qx2), fminf(qy1, qy2)), fminf(qz1, qz2));
-	const float tf = fminf(fminf(fmaxf(qx1, qx2), fmaxf(qy1, qy2)), fmaxf(qz1, qz2));
-	const float s = 2.0f * F.amax + 0x1p-20f * (fabsf(tn) + fabsf(tf));
-	return tf - tn < -s || tf + s < (float)RT_RAY_EPSILON;
+	float e;
+	const int r = boxf(b.lo, b.hi, F, e);
+	return r == 0 || (r == 1 && e > limf);
 }
 
 // What a primitive's intersectLocal leaves in the isect (object space).

@@ -42,7 +42,7 @@ struct alignas(64) DNode2f {
 struct alignas(32) DItemBox {
 	float lo[3], hi[3];
 	int32_t obj;
-	int32_t pad;
+	int32_t type; // rt_object_type of obj: the split shadow stage queues candidates by primitive kind without reading the object
 };
 #define RT_REF_MESH_EXIT ((int32_t)0x80000000)
 #define RT_REF_NONE ((int32_t)0x80000001)

@@ -24,7 +24,8 @@
 
 namespace rtd {
 
-enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1 };
+enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1,
+       TRAV_SCAN = 2 }; // candidate listing for the split shadow stage (rt_scan.cuh): no primitive is tested during the walk
 
 // Work counters for the cost model (scenes/cost_model.py): host build of tests/hostsim only.
 #if defined(RT_COUNT_WORK) && !defined(__CUDACC__)
@@ -176,8 +177,7 @@ RT_COLD void emit_face(const DScene& S, int obj, unsigned rank, int pos, double 
 	sbuf_add(B, t, ((unsigned long long)rank << 32) | (unsigned)pos, dot(N, dw) > 0, trans, kt);
 }
 
-// State of a walk that is inside a mesh (level 1); kept in one struct so that the cold
-// enter/leave code can live in real functions.
+// State of a walk that is inside a mesh (level 1).
 struct MeshVisit {
 	double len;      // |M^-1 d|: t_world = t_local / len
 	int obj, rank;   // the scene-level candidate being visited
@@ -187,191 +187,309 @@ struct MeshVisit {
 	int best_pos;
 };
 
+// ---- the walk, split in two -------------------------------------------------------------------
+// HOT: the node loop.  Everything it needs is single precision and lives in registers: the ray's float
+// image (RayF), the float node array, the limit rounded UP to float, the stack of (reference, float
+// entry distance) pairs - one 8-byte store per push.  No double-precision instruction and no local
+// memory access other than the stack itself.
+// COLD: everything that needs the reference's FP64 arithmetic - ambiguous boxes, leaf candidates,
+// entering and leaving a mesh - is out of line and works on `Walk`, the double-precision side of the
+// ray, which lives in local memory and is touched at leaves only (a walk visits ~10 nodes per leaf).
+struct StackEnt {
+	int ref;
+	float e;
+};
+struct Walk {
+	d3 ow, dw;           // the ray, world space
+	d3 o, d;             // the ray in the current space (world at level 0, the mesh's object space at level 1)
+	RayInv I;            // its double-precision inverse
+	double lim;          // best t so far / shadow cut, current space
+	double lim0;         // TRAV_SCAN: the fixed world-space limit of the listing walk
+	MeshVisit V;
+	const DNode2* nodes; // double images of the current tree's nodes
+	const DTri* tris;    // the current mesh's triangles
+	TravClosest* C;
+	SBuf* B;
+	int mode;
+	bool prune;
+};
+
+// set-up: inverse, float image, root box.  Returns the first reference to visit (RT_REF_NONE: the
+// ray misses the scene's box)
+RT_COLD int walk_begin(const DScene& S, Walk& W, RayF& F, float& limf)
+{
+	W.o = W.ow;
+	W.d = W.dw;
+	make_inv(W.I, F, W.o, W.d, W.prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
+	W.nodes = S.snodes2;
+	W.tris = S.tris;
+	W.lim = W.mode == TRAV_CLOSEST ? RT_T_INF : (W.mode == TRAV_SHADOW ? W.B->cut : W.lim0);
+	limf = f_up(W.lim);
+	W.V.len = 1.0;
+	W.V.obj = -1;
+	W.V.rank = 0;
+	W.V.item_off = 0;
+	W.V.have = false;
+	W.V.best_t = RT_T_INF;
+	W.V.best_pos = 0x7fffffff;
+	double e;
+	if (!box_hit(S.stree.lo, S.stree.hi, W.o, W.d, W.I, e)) return RT_REF_NONE;
+	return S.stree.root;
+}
+
+// a child of node `cur` whose float test was ambiguous: the reference's decision from the double box.
+// Returned by value ({hit, entry distance}) so that the node loop's variables never have their address taken.
+RT_COLD StackEnt walk_resolve(const Walk& W, int cur, int child)
+{
+	const DNode2& n = W.nodes[cur];
+	StackEnt r;
+	r.ref = boxf_resolve(child ? n.lo1 : n.lo0, child ? n.hi1 : n.hi0, W.o, W.d, W.I, r.e);
+	return r;
+}
+
+// one 64-byte float node through the read-only path, four 128-bit loads
+RT_HD DNode2f ld_node2f(const DNode2f* p)
+{
+#if defined(__CUDA_ARCH__) && !defined(RT_NODE_PLAIN_LOAD)
+	const float4* q = reinterpret_cast<const float4*>(p);
+	const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+	DNode2f n;
+	n.lo0[0] = a.x; n.lo0[1] = a.y; n.lo0[2] = a.z; n.hi0[0] = a.w;
+	n.hi0[1] = b.x; n.hi0[2] = b.y; n.lo1[0] = b.z; n.lo1[1] = b.w;
+	n.lo1[2] = c.x; n.hi1[0] = c.y; n.hi1[1] = c.z; n.hi1[2] = c.w;
+	n.c0 = __float_as_int(d.x); n.c1 = __float_as_int(d.y);
+	n.pad[0] = n.pad[1] = 0;
+	return n;
+#else
+	return *p;
+#endif
+}
+
+// a mesh leaf: its (at most three) triangles
+template <int FIXED_MODE> RT_COLD void walk_leaf_tris(const DScene& S, Walk& W, int first, int count, float& limf, int& sp)
+{
+	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : W.mode;
+#pragma unroll 1
+	for (int i = 0; i < count; i++) {
+		const int pos = first + i;
+		double t;
+		d3 bary;
+		RT_CNT(tris, mode);
+		if (!tri_hit<false>(W.tris[pos], W.o, W.d, t, bary)) continue;
+		if (mode == TRAV_CLOSEST) {
+			MeshVisit& V = W.V;
+			if (!V.have || t < V.best_t || (t == V.best_t && pos < V.best_pos)) {
+				V.have = true;
+				V.best_t = t;
+				V.best_pos = pos;
+				if (t < W.lim) W.lim = t;
+			}
+		} else {
+			emit_face(S, W.V.obj, (unsigned)W.V.rank, pos, W.V.len, W.o, W.d, W.dw, *W.B);
+			if (W.B->dead) { sp = 0; break; } // any-hit exit (rt_shadow.cuh): leave through the pop section's one way out
+			W.lim = lim_to_local(W.B->cut, W.V.len);
+		}
+	}
+	limf = f_up(W.lim);
+}
+
+// A trimesh candidate (item i of the scene leaf [first, first + count)) is ENTERED: the rest of the leaf and an
+// exit marker go on the stack and the walk continues in the mesh's object space (L = the ray there).
+// Returns the mesh's root reference, or RT_REF_NONE when the ray misses the root box.
+RT_COLD int walk_enter_mesh(const DScene& S, Walk& W, const LocalRay& L, int first, int count, int i, RayF& F, const DNode2f*& nodesf, int& level, int& sp, StackEnt* stk)
+{
+	const int rank = first + i;
+	const int obj = S.sboxf[rank].obj;
+	const rt_object& ob = S.objs[obj];
+	if (i + 1 < count) { stk[sp].ref = leaf_ref(rank + 1, count - i - 1); stk[sp].e = -INFINITY; sp++; }
+	stk[sp].ref = RT_REF_MESH_EXIT;
+	stk[sp].e = -INFINITY;
+	sp++;
+	const DTree& T = S.mtrees[ob.mesh];
+	MeshVisit& V = W.V;
+	V.obj = obj;
+	V.rank = rank;
+	V.len = L.len;
+	V.item_off = (int)S.meshes[ob.mesh].item_off;
+	V.have = false;
+	V.best_t = RT_T_INF;
+	V.best_pos = 0x7fffffff;
+	W.tris = S.tris + V.item_off;
+	W.nodes = S.mnodes2 + T.node_off;
+	nodesf = S.mnodes2f + T.node_off;
+	W.o = L.o;
+	W.d = L.d;
+	make_inv(W.I, F, W.o, W.d, W.prune ? S.mesh_slack[ob.mesh] : 0.0, S.mesh_slack[ob.mesh] * 1e9);
+	level = 1;
+	W.lim = lim_to_local(W.lim, V.len);
+	double er;
+	if (box_hit(T.lo, T.hi, W.o, W.d, W.I, er) && !(W.prune && er > W.lim)) return T.root;
+	return RT_REF_NONE;
+}
+
+// a scene-level leaf: the candidates (bit i of `pend`) that the float test of their boxes could not
+// rule out.  Two passes: first the reference's own box test of all of them (Geometry::intersect's
+// world-bbox pretest, scene.cpp:15,43 - a real filter, leaf boxes are unions), then the object-space
+// tests of the survivors; postponing a test can only weaken the distance cull, never the result.
+// A trimesh candidate is ENTERED: the rest of the leaf and an exit marker go on the stack and the
+// walk continues in the mesh's object space; the return value is the mesh's root reference then.
+template <int FIXED_MODE> RT_COLD int walk_leaf_items(const DScene& S, Walk& W, int first, int count, unsigned pend, RayF& F, const DNode2f*& nodesf, float& limf, int& level, int& sp, StackEnt* stk)
+{
+	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : W.mode;
+	unsigned keep = 0;
+#pragma unroll 1
+	while (pend) {
+		const int i = rt_ffs(pend) - 1;
+		pend &= pend - 1;
+		const rt_object& ob = S.objs[S.sboxf[first + i].obj];
+		double eb;
+		if (!box_hit(ob.bbox, ob.bbox + 3, W.o, W.d, W.I, eb)) continue;
+		if (W.prune && eb > W.lim) continue;
+		keep |= 1u << i;
+	}
+	int next = RT_REF_NONE;
+#pragma unroll 1
+	while (keep) {
+		const int i = rt_ffs(keep) - 1;
+		keep &= keep - 1;
+		const int rank = first + i;
+		const int obj = S.sboxf[rank].obj;
+		const rt_object& ob = S.objs[obj];
+		LocalRay L;
+		to_local(L, ob, W.o, W.d);
+		if (ob.type == RT_OBJ_TRIMESH) {
+			next = walk_enter_mesh(S, W, L, first, count, i, F, nodesf, level, sp, stk);
+			break;
+		}
+		if (mode == TRAV_CLOSEST) {
+			prim_closest(ob, L, rank, obj, *W.C);
+			if (W.C->have) W.lim = W.C->best_t;
+		} else {
+			prim_list(S, ob, L, W.dw, rank, *W.B);
+			if (W.B->dead) { sp = 0; break; } // any-hit exit, as above
+			W.lim = W.B->cut;
+		}
+	}
+	limf = f_up(W.lim);
+	return next;
+}
+
+// the exit marker of a mesh visit: Trimesh::intersectLocal's winner goes back to the scene level as
+// ONE candidate, and the walk returns to world space
+template <int FIXED_MODE> RT_COLD void walk_mesh_exit(const DScene& S, Walk& W, RayF& F, const DNode2f*& nodesf, float& limf, int& level, int sp)
+{
+	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : W.mode;
+	const MeshVisit& V = W.V;
+	TravClosest& C = *W.C; // (not dereferenced by the other modes)
+	if (mode == TRAV_CLOSEST && V.have) {
+		const double t = V.best_t / V.len;
+		if (!C.have || t < C.best_t || (t == C.best_t && V.rank < C.best_rank)) {
+			C.have = true;
+			C.best_t = t;
+			C.best_rank = V.rank;
+			C.best_obj = V.obj;
+			C.best_fpos = V.item_off + V.best_pos;
+		}
+	}
+	W.o = W.ow;
+	W.d = W.dw;
+	// the world-space inverse again (recomputed: a walk rarely returns), unless nothing is left to test with it
+	if (sp > 0) make_inv(W.I, F, W.o, W.d, W.prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
+	W.nodes = S.snodes2;
+	nodesf = S.snodes2f;
+	level = 0;
+	W.lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : (mode == TRAV_SHADOW ? W.B->cut : W.lim0);
+	limf = f_up(W.lim);
+}
+
 // FIXED_MODE >= 0 compiles the walk for one query kind only (the wavefront's stage kernels).
-// budget > 0: give up after that many tree nodes and return false - the caller hands the ray to the
-// warp-cooperative walk (rt_coop.cuh).  A few rays visit thousands of nodes (a zero direction
+// budget > 0: give up after that many stack pops (subtrees) and return false - the caller hands the ray
+// to the warp-cooperative walk (rt_coop.cuh).  A few rays visit thousands of nodes (a zero direction
 // component makes the reference's slab test accept every box along that axis, bbox.cc:43) and a
 // warp waits for its slowest lane; the result of an abandoned walk is not used.
+// All ways out of the loop are in the pop section: a second exit inside the node or leaf loops costs
+// the warp its reconvergence points (profiles/r1_variants.txt: 3x slower).
 template <bool PRUNE, int FIXED_MODE = -1>
 RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B, int budget = 0)
 {
 	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : mode_arg;
 	RT_WORK_SCOPE(mode);
-	int stk[RT_STACK];
-	double stke[RT_STACK];
 	const bool prune = PRUNE || mode == TRAV_SHADOW;
-	// current space (world at level 0, the mesh's object space at level 1)
-	d3 o = ow, d = dw;
-	RayInv I;
+	Walk W;
+	W.ow = ow;
+	W.dw = dw;
+	W.C = &C;
+	W.B = &B;
+	W.mode = mode;
+	W.prune = prune;
+	StackEnt stk[RT_STACK];
 	RayF F;
-	make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
-	const DNode2* nodes = S.snodes2;
+	float limf;
 	const DNode2f* nodesf = S.snodes2f;
-	const DTri* tris = S.tris;
 	int level = 0;
-	double lim = mode == TRAV_CLOSEST ? RT_T_INF : B.cut;
-	MeshVisit V;
-	V.len = 1.0;
-	V.obj = -1;
-	V.rank = 0;
-	V.item_off = 0;
-	V.have = false;
-	V.best_t = RT_T_INF;
-	V.best_pos = 0x7fffffff;
-	double e;
-	if (!box_hit(S.stree.lo, S.stree.hi, o, d, I, e)) return true;
 	int sp = 0;
-	int cur = S.stree.root;
+	int cur = walk_begin(S, W, F, limf);
+	if (cur == RT_REF_NONE) return true;
+	bool done = true;
 	for (;;) {
 		// ---- 1. internal nodes: test both children, go near, push far ---------------------------
 #pragma unroll 1
 		while (cur >= 0) {
-			const DNode2f& nf = nodesf[cur];
+			const DNode2f nf = ld_node2f(nodesf + cur);
 			RT_CNT(nodes, mode);
-			if (budget > 0 && --budget == 0) return false;
-			const int c0 = nf.c0, c1 = nf.c1;
-			double e0, e1;
-			bool h0, h1;
-			box2_hit(nf, nodes[cur], o, d, I, F, h0, h1, e0, e1);
-			if (prune) { h0 = h0 && !(e0 > lim); h1 = h1 && !(e1 > lim); }
+			float e0, e1;
+			int r0 = boxf(nf.lo0, nf.hi0, F, e0);
+			int r1 = boxf(nf.lo1, nf.hi1, F, e1);
+			if (r0 == 2) { const StackEnt r = walk_resolve(W, cur, 0); r0 = r.ref; e0 = r.e; }
+			if (r1 == 2) { const StackEnt r = walk_resolve(W, cur, 1); r1 = r.ref; e1 = r.e; }
+			bool h0 = r0 != 0, h1 = r1 != 0;
+			if (prune) { h0 = h0 && !(e0 > limf); h1 = h1 && !(e1 > limf); }
 			if (h0 && h1) {
 				const bool swap = prune && e1 < e0;
-				stk[sp] = swap ? c0 : c1;
-				stke[sp] = swap ? e0 : e1;
+				stk[sp].ref = swap ? nf.c0 : nf.c1;
+				stk[sp].e = swap ? e0 : e1;
 				sp++;
-				cur = swap ? c1 : c0;
-			} else if (h0) cur = c0;
-			else if (h1) cur = c1;
-			else cur = RT_REF_NONE;
+				cur = swap ? nf.c1 : nf.c0;
+			} else cur = h0 ? nf.c0 : (h1 ? nf.c1 : RT_REF_NONE);
 		}
 		// ---- 2. a leaf --------------------------------------------------------------------------
 		if (cur != RT_REF_NONE) {
 			const int first = leaf_first(cur), count = leaf_count(cur);
 			cur = RT_REF_NONE;
 			if (level == 1) {
-#pragma unroll 1
-				for (int i = 0; i < count; i++) {
-					const int pos = first + i;
-					double t;
-					d3 bary;
-					RT_CNT(tris, mode);
-					if (!tri_hit<false>(tris[pos], o, d, t, bary)) continue;
-					if (mode == TRAV_CLOSEST) {
-						if (!V.have || t < V.best_t || (t == V.best_t && pos < V.best_pos)) {
-							V.have = true;
-							V.best_t = t;
-							V.best_pos = pos;
-							if (t < lim) lim = t;
-						}
-					} else {
-						emit_face(S, V.obj, (unsigned)V.rank, pos, V.len, o, d, dw, B);
-						if (B.dead) { sp = 0; break; } // any-hit exit (rt_shadow.cuh), through the pop section's one way out: a second
-						                               // return inside the loop costs the warp its reconvergence points (3x slower)
-						lim = lim_to_local(B.cut, V.len);
-					}
-				}
+				walk_leaf_tris<FIXED_MODE>(S, W, first, count, limf, sp);
 			} else {
-				// two passes over the leaf's (at most three) candidates: first the box tests of all of
-				// them, then the object-space tests of the survivors.  The lanes of a warp that have ANY
-				// survivor then run the long primitive code together, instead of only those whose i-th
-				// candidate survived.  Postponing a test can only weaken the distance cull, never the result.
+				// float images of the candidates' boxes first (32 bytes each): what is certainly missed, or
+				// certainly entered beyond the limit, never reaches the double-precision code
 				unsigned pend = 0;
 #pragma unroll 1
 				for (int i = 0; i < count; i++) {
-					const DItemBox& ib = S.sboxf[first + i];
 					RT_CNT(objs, mode);
-					if (box_miss_f(ib, F)) continue;
-					const rt_object& ob = S.objs[ib.obj];
-					// Geometry::intersect / intersectList: world-bbox pretest (scene.cpp:15,43) is a real
-					// filter (leaf boxes are unions), then the object-space test
-					double eb;
-					if (!box_hit(ob.bbox, ob.bbox + 3, o, d, I, eb)) continue;
-					if (prune && eb > lim) continue;
-					pend |= 1u << i;
+					if (!box_miss_f(S.sboxf[first + i], F, prune ? limf : INFINITY)) pend |= 1u << i;
 				}
-#pragma unroll 1
-				while (pend) {
-					const int i = rt_ffs(pend) - 1;
-					pend &= pend - 1;
-					const int rank = first + i;
-					const int obj = S.sboxf[rank].obj;
-					const rt_object& ob = S.objs[obj];
-					LocalRay L;
-					to_local(L, ob, o, d);
-					if (ob.type == RT_OBJ_TRIMESH) {
-						// enter the mesh: remainder of this leaf, then the exit marker, then the mesh's nodes
-						if (i + 1 < count) { stk[sp] = leaf_ref(rank + 1, count - i - 1); stke[sp] = -RT_T_INF; sp++; }
-						stk[sp] = RT_REF_MESH_EXIT;
-						stke[sp] = -RT_T_INF;
-						sp++;
-						const DTree& T = S.mtrees[ob.mesh];
-						V.obj = obj;
-						V.rank = rank;
-						V.len = L.len;
-						V.item_off = (int)S.meshes[ob.mesh].item_off;
-						V.have = false;
-						V.best_t = RT_T_INF;
-						V.best_pos = 0x7fffffff;
-						tris = S.tris + V.item_off;
-						nodes = S.mnodes2 + T.node_off;
-						nodesf = S.mnodes2f + T.node_off;
-						o = L.o;
-						d = L.d;
-						make_inv(I, F, o, d, prune ? S.mesh_slack[ob.mesh] : 0.0, S.mesh_slack[ob.mesh] * 1e9);
-						level = 1;
-						lim = lim_to_local(lim, V.len);
-						double er;
-						if (box_hit(T.lo, T.hi, o, d, I, er) && !(prune && er > lim)) cur = T.root;
-						break;
-					}
-					if (mode == TRAV_CLOSEST) {
-						prim_closest(ob, L, rank, obj, C);
-						if (C.have) lim = C.best_t;
-					} else {
-						prim_list(S, ob, L, dw, rank, B);
-						if (B.dead) { sp = 0; break; } // any-hit exit (rt_shadow.cuh), through the pop section's one way out: a second
-						                               // return inside the loop costs the warp its reconvergence points (3x slower)
-						lim = B.cut;
-					}
-				}
+				if (pend) cur = walk_leaf_items<FIXED_MODE>(S, W, first, count, pend, F, nodesf, limf, level, sp, stk);
 			}
 		}
 		// ---- 3. pop -----------------------------------------------------------------------------
 		if (cur == RT_REF_NONE) {
 #pragma unroll 1
 			for (;;) {
-				if (sp == 0) return true;
+				if (sp == 0) break;
+				if (--budget == 0) { done = false; break; }
 				sp--;
-				const int a = stk[sp];
-				if (a == RT_REF_MESH_EXIT) {
-					// Trimesh::intersectLocal's winner goes back to the scene level as one candidate
-					if (mode == TRAV_CLOSEST && V.have) {
-						const double t = V.best_t / V.len;
-						if (!C.have || t < C.best_t || (t == C.best_t && V.rank < C.best_rank)) {
-							C.have = true;
-							C.best_t = t;
-							C.best_rank = V.rank;
-							C.best_obj = V.obj;
-							C.best_fpos = V.item_off + V.best_pos;
-						}
-					}
-					o = ow;
-					d = dw;
-					// world-space inverse again (recomputed: keeping a copy costs more in spills), unless
-					// nothing is left to test with it
-					if (sp > 0) make_inv(I, F, o, d, prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
-					nodes = S.snodes2;
-					nodesf = S.snodes2f;
-					level = 0;
-					lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : B.cut;
+				const StackEnt a = stk[sp];
+				if (a.ref == RT_REF_MESH_EXIT) {
+					walk_mesh_exit<FIXED_MODE>(S, W, F, nodesf, limf, level, sp);
 					continue;
 				}
-				if (prune && stke[sp] > lim) continue;
-				cur = a;
+				if (prune && a.e > limf) continue;
+				cur = a.ref;
 				break;
 			}
+			if (cur == RT_REF_NONE) break;
 		}
 	}
+	return done;
 }
 
 // Scene::intersect.  On return out.obj/out.fpos/out.t identify the winner; finalize_hit fills the rest.

@@ -30,13 +30,13 @@ struct rt_ctx {
 	int sm_count = 0;
 	int pool_blocks = 0;
 	// work buffers (grown on demand, reused across calls)
-	void* buf[48] = {nullptr};
-	size_t buf_bytes[48] = {0};
+	void* buf[64] = {nullptr};
+	size_t buf_bytes[64] = {0};
 	unsigned long long launches = 0;
 	// wavefront path
 	long long wave_width = 0;              // rays per round; 0 = chosen per call from the memory budget below (RT_B200_WAVE overrides)
 	size_t queue_budget = 0;               // bytes the ray queues of a round may take: a quarter of the device memory
-	int walk_budget = 96;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
+	int walk_budget = 40;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
 	int n_area_lights = 0;                 // area + spot lights of the uploaded scene
 	bool budget_auto = true;               // no RT_B200_BUDGET given: the budget adapts to the scene
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
@@ -46,6 +46,8 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
+	bool shadow_split = true;              // the shadow stage as listing walk + per-kind candidate kernels (device/rt_scan.cuh); RT_B200_SPLIT=0: one kernel
+	bool kind_present[6] = {false, false, false, false, false, false}; // primitive kinds of the uploaded scene (a queue and a launch per kind present)
 	unsigned long long rounds = 0;
 	// optional per-stage timing
 	bool profile = false;
@@ -59,8 +61,9 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
+       B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
        B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_COUNT };
-static_assert(B_COUNT <= 48, "rt_ctx::buf too small");
+static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
 	do {                                                                                                  \
@@ -128,6 +131,28 @@ rt_status make_queue(rt_ctx* ctx, int bd, int bi, long long cap, int nd, RayQueu
 
 rt_status launch_pool(rt_ctx* ctx, PoolArgs& A);
 
+// Queues of the split shadow stage for up to `rays` shadow rays per round: three candidates per ray for the
+// common analytic kinds, four leaf triangles; a ray whose candidate finds its queue full takes the complete walk.
+rt_status make_cand_queues(rt_ctx* ctx, long long rays, CandQueues& Q)
+{
+	static const int mult[CQ_KINDS] = {3, 3, 1, 3, 1, 4};
+	rt_status st;
+	if ((st = ensure(ctx, B_SH_SIDE, (size_t)rays * sizeof(ShadowSide))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_SH_FLAGS, (size_t)rays * sizeof(unsigned))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_CQ_LIST, (size_t)rays * sizeof(int))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_CQ_CNT, 64)) != RT_OK) return st;
+	for (int k = 0; k < CQ_KINDS; k++) {
+		Q.cap[k] = ctx->kind_present[k] ? (unsigned long long)rays * mult[k] : 0ull;
+		if ((st = ensure(ctx, B_CQ0 + k, (size_t)Q.cap[k] * (k == RT_OBJ_TRIMESH ? sizeof(uint4) : sizeof(uint2)))) != RT_OK) return st;
+		if (k == RT_OBJ_TRIMESH) Q.tri = (uint4*)ctx->buf[B_CQ0 + k];
+		else Q.q[k] = (uint2*)ctx->buf[B_CQ0 + k];
+	}
+	Q.count = (unsigned long long*)ctx->buf[B_CQ_CNT];
+	Q.n_complex = Q.count + CQ_KINDS;
+	Q.complex_list = (int*)ctx->buf[B_CQ_LIST];
+	return RT_OK;
+}
+
 cudaEvent_t next_event(rt_ctx* ctx)
 {
 	if (ctx->ev_used == ctx->ev_pool.size()) {
@@ -148,6 +173,26 @@ cudaEvent_t next_event(rt_ctx* ctx)
 	} while (0)
 #define STAGE(id, ...) STAGE_ON(ctx->stream, id, __VA_ARGS__)
 
+// One round's shadow rays through the split stage (device/rt_scan.cuh): listing walk, one candidate kernel per
+// primitive kind present in the scene, resolve, and the complete walk for what is left.
+rt_status launch_shadow_split(rt_ctx* ctx, const PoolArgs& A, const RayQueue& SQ, int par, WaveCounters* cnt, long long max_rays, const CandQueues& Q, cudaStream_t s)
+{
+	ShadowSide* side = (ShadowSide*)ctx->buf[B_SH_SIDE];
+	unsigned* flags = (unsigned*)ctx->buf[B_SH_FLAGS];
+	CK(cudaMemsetAsync(Q.count, 0, 64, s));
+	STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_scan<<<blocks_for(max_rays, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, s>>>(ctx->S, SQ, par, cnt, side, flags, Q));
+	const unsigned pgrid = (unsigned)ctx->sm_count * 8u; // persistent grids over the device-side counts
+	if (ctx->kind_present[RT_OBJ_SPHERE]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_SPHERE><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
+	if (ctx->kind_present[RT_OBJ_BOX]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_BOX><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
+	if (ctx->kind_present[RT_OBJ_SQUARE]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_SQUARE><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
+	if (ctx->kind_present[RT_OBJ_CYLINDER]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_CYLINDER><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
+	if (ctx->kind_present[RT_OBJ_CONE]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_CONE><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
+	if (ctx->kind_present[RT_OBJ_TRIMESH]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_TRIMESH><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
+	STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_resolve<<<blocks_for(max_rays, 256), 256, 0, s>>>(A, SQ, par, cnt, flags, Q));
+	STAGE_ON(s, RT_STAGE_SHADOW, k_wave_shadow_list<<<(unsigned)ctx->sm_count * RT_SHADOW_MINB, RT_TRACE_THREADS, 0, s>>>(ctx->S, A, SQ, Q));
+	return RT_OK;
+}
+
 // The trace loop over n_slots primary-ray slots as a streaming wavefront (device/rt_wave.cuh).
 rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 {
@@ -160,7 +205,8 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	// bytes per ray of the round, so the width is what a quarter of the device memory holds, at most 32 Mi.
 	long long W = ctx->wave_width;
 	if (W <= 0) {
-		const size_t per_ray = 4 * 104 + 2 * (size_t)(L > 0 ? L : 1) * 80 + 24;
+		// + per shadow ray of the split shadow stage: side record, flags, list entry and the candidate queues (launch_shadow_split)
+		const size_t per_ray = 4 * 104 + 2 * (size_t)(L > 0 ? L : 1) * 80 + 24 + (ctx->shadow_split ? (size_t)(L > 0 ? L : 1) * 200 : 0);
 		W = (long long)(ctx->queue_budget / per_ray) / 1024 * 1024;
 		// the spill stack (allocated only if a round ever has more than W children) may take another half of the memory
 		const long long spill_fit = (long long)(2 * ctx->queue_budget / (((size_t)(A.depth < 30 ? A.depth : 30) + 2) * 104)) / 1024 * 1024;
@@ -179,6 +225,10 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if ((st = make_queue(ctx, B_SQ2_D, B_SQ2_I, W * (L > 0 ? L : 1), 9, sq[1])) != RT_OK) return st;
 	// per-stage profiling wants clean kernel times: no overlap then
 	const bool overlap = ctx->overlap && !ctx->profile;
+	const bool split = ctx->shadow_split && L > 0;
+	CandQueues CQ;
+	std::memset(&CQ, 0, sizeof(CQ));
+	if (split && (st = make_cand_queues(ctx, W * L, CQ)) != RT_OK) return st;
 	bool shadow_pending[2] = {false, false};
 	long long round = 0;
 	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
@@ -247,13 +297,17 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		if (L > 0) {
-			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
+			// the split stage's queues are shared by both parities: its pipelines follow one another on one stream
+			cudaStream_t sstream = overlap ? ctx->stream2[split ? 0 : par] : ctx->stream;
 			if (overlap) {
 				CK(cudaEventRecord(ctx->ev_shade[par], ctx->stream));
 				CK(cudaStreamWaitEvent(sstream, ctx->ev_shade[par], 0));
 			}
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
-			STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt));
+			if (split) {
+				if ((st = launch_shadow_split(ctx, A, sq[par], par, cnt, m * L, CQ, sstream)) != RT_OK) return st;
+			} else
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt));
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
@@ -271,6 +325,12 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		cur = nxt;
 		nxt = tmp;
 		ctx->rounds++;
+	}
+	if (split && getenv("RT_B200_DEBUG")) {
+		unsigned long long h[8];
+		cudaDeviceSynchronize();
+		cudaMemcpy(h, CQ.count, 64, cudaMemcpyDeviceToHost);
+		fprintf(stderr, "[rt_b200] last round: candidates sphere %llu box %llu square %llu cylinder %llu cone %llu triangle %llu, complex rays %llu\n", h[0], h[1], h[2], h[3], h[4], h[5], h[6]);
 	}
 	// everything that follows on the main stream (resolve kernels, the frame copy) needs the last shadow rays
 	for (int par = 0; par < 2; par++)
@@ -355,6 +415,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (cudaMallocHost((void**)&ctx->pinned, 64) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	if (const char* e = getenv("RT_B200_WAVE")) { const long long v = atoll(e); if (v >= 1024) ctx->wave_width = (v + 1023) / 1024 * 1024; }
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_SPLIT")) ctx->shadow_split = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;
@@ -373,7 +434,7 @@ void rt_destroy(rt_ctx* ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	free_scene(ctx);
-	for (int i = 0; i < 48; i++)
+	for (int i = 0; i < 64; i++)
 		if (ctx->buf[i]) cudaFree(ctx->buf[i]);
 	for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
 	if (ctx->pinned) cudaFreeHost(ctx->pinned);
@@ -452,6 +513,14 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	for (uint64_t k = 0; k < A.count(RT_SEC_LIGHTS); k++) {
 		if (lights[k].type < RT_LIGHT_DIRECTIONAL || lights[k].type > RT_LIGHT_SPOT) { ctx->error = "unknown light type"; return RT_ERR_ARG; }
 		if (lights[k].type >= RT_LIGHT_AREA_RECT) n_area++;
+	}
+	{
+		const rt_object* objs = A.ptr<rt_object>(RT_SEC_OBJECTS);
+		for (int k = 0; k < 6; k++) ctx->kind_present[k] = false;
+		for (uint64_t k = 0; k < A.count(RT_SEC_OBJECTS); k++) {
+			if (objs[k].type < RT_OBJ_SPHERE || objs[k].type > RT_OBJ_TRIMESH) { ctx->error = "unknown object type"; return RT_ERR_ARG; }
+			ctx->kind_present[objs[k].type] = true;
+		}
 	}
 	const long long n_snodes = (long long)A.count(RT_SEC_SCENE_NODES), n_mnodes = (long long)A.count(RT_SEC_MESH_NODES);
 	const long long n_mitems = (long long)A.count(RT_SEC_MESH_ITEMS), n_sitems = (long long)A.count(RT_SEC_SCENE_ITEMS);
@@ -535,7 +604,7 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	CK(cudaStreamSynchronize(ctx->stream)); // also: the caller may reuse `arena` on return
 	if (hflags[0]) { ctx->error = "invalid arena: index out of range (device check " + std::to_string(hflags[0]) + ")"; return RT_ERR_ARG; }
 	if ((hflags[1] | hflags[2]) & 0x80000000u || hflags[1] + hflags[2] > RT_STACK - 4) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
-	if (ctx->budget_auto) ctx->walk_budget = 96;
+	if (ctx->budget_auto) ctx->walk_budget = 40;
 	ctx->n_area_lights = n_area;
 	ctx->has_scene = true;
 	return RT_OK;

@@ -312,3 +312,25 @@ def test_bench_reference_arm_prints_one_json_line():
     assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "workload" in d["config"] and d["metric"].startswith("Mrays/s")
+
+
+@pytest.mark.parametrize("gen", ["dragon", "mixed"])
+def test_full_size_arena_hashes(rtlib, tmp_path, gen):
+    """The loader pinned at FULL size: tests/golden/arena_hashes.json holds sha256 and size of the arena flattened
+    out of the reference's OWN parse + KdTree build (std::sort permutation included) of the full dragon stand-in
+    (869,556 faces) and the full 1M-primitive scene (tests/golden/make_arena_hashes.py: half an hour of CPU per
+    scene, run once).  rt_load_ray_file must reproduce them byte for byte - which is what makes ref_load_arena
+    (full-size parity tests, CPU timing legs) a proven shortcut."""
+    import hashlib
+    import json
+    import gen_scenes
+    with open(os.path.join(ROOT, "tests", "golden", "arena_hashes.json")) as f:
+        want = json.load(f)[gen]
+    text = gen_scenes.GENERATORS[gen](want["scale"])
+    assert len(text) == want["text_bytes"] and hashlib.sha256(text.encode()).hexdigest() == want["text_sha256"], "generator changed"
+    path = tmp_path / (gen + ".ray")
+    path.write_text(text)
+    arena = rtlib.load_ray_file(str(path))
+    data = arena.bytes()
+    assert len(data) == want["arena_bytes"]
+    assert hashlib.sha256(data).hexdigest() == want["arena_sha256"]

@@ -46,7 +46,8 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
-	bool shadow_split = true;              // the shadow stage as listing walk + per-kind candidate kernels (device/rt_scan.cuh); RT_B200_SPLIT=0: one kernel
+	bool shadow_split = false;             // RT_B200_SPLIT=1: the shadow stage as listing walk + per-kind candidate kernels (device/rt_scan.cuh).
+	                                       // Measured SLOWER than the one-kernel walk (profiles/r2_variants.txt: no any-hit exit in the listing walk), kept for A/B
 	bool kind_present[6] = {false, false, false, false, false, false}; // primitive kinds of the uploaded scene (a queue and a launch per kind present)
 	unsigned long long rounds = 0;
 	// optional per-stage timing

@@ -93,6 +93,8 @@ def lib():
                                    ctypes.POINTER(vp), ctypes.POINTER(Stats)]
     L.rt_trace_pixels.argtypes = [vp, ctypes.POINTER(Params), ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, vp]
     L.rt_trace_rays.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, ctypes.c_int, vp, vp]
+    L.rt_intersect_static.argtypes = [vp, vp, ctypes.c_int, vp]
+    L.rt_intersect_static.restype = i32
     L.rt_selftest_division.argtypes = [vp, ctypes.c_longlong, ctypes.c_ulonglong, ctypes.c_int, ctypes.POINTER(ctypes.c_ulonglong)]
     L.rt_selftest_division.restype = i32
     L.rt_selftest_derive.argtypes = [vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_ulonglong)]
@@ -281,6 +283,13 @@ class Context:
         out = np.zeros((len(ij), 3))
         self._check(lib().rt_trace_pixels(self._h, ctypes.byref(params), w, h, ij.ctypes.data, len(ij), out.ctypes.data))
         return out
+
+    def intersect_static(self, rays):
+        """rt_intersect_static: Scene::intersect for at most STATIC_MAX_RAYS rays, no device allocation."""
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 6)
+        hits = np.zeros(len(rays), HIT_DTYPE)
+        self._check(lib().rt_intersect_static(self._h, rays.ctypes.data, len(rays), hits.ctypes.data))
+        return hits
 
     def trace_rays(self, params, rays, depth, want_hits=True, want_rgb=True):
         rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 6)

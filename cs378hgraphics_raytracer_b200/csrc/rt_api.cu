@@ -50,6 +50,7 @@ struct rt_ctx {
 	                                       // Measured SLOWER than the one-kernel walk (profiles/r2_variants.txt: no any-hit exit in the listing walk), kept for A/B
 	bool kind_present[6] = {false, false, false, false, false, false}; // primitive kinds of the uploaded scene (a queue and a launch per kind present)
 	unsigned long long rounds = 0;
+	void* static_scratch = nullptr;        // device address of g_static_scratch on this context's GPU (rt_intersect_static)
 	// optional per-stage timing
 	bool profile = false;
 	std::vector<cudaEvent_t> ev_pool;
@@ -890,6 +891,68 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
 	return read_stats(ctx, nullptr, 0.f);
 }
 
+
+// ---- rt_intersect_static: Scene::intersect for a small batch of rays WITHOUT any device allocation ------------
+// (no counterpart in the reference; added for callers that cannot call
+// cudaMalloc: code under CUDA graph capture, tight serving loops.)  What rt_trace_rays stages in cudaMalloc'ed
+// work buffers - the rays on their way in, the hit records on their way out - lives in ONE file-scope device
+// array of a fixed size instead.  Every GPU that loads the library holds these RT_STATIC_SCRATCH_BYTES until exit.
+//   layout: [0, MAX * sizeof(rt_ray))  rays     [MAX * sizeof(rt_ray), ... + MAX * sizeof(rt_hit))  hit records
+// In host code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is asked
+// for once per context (= once per device, with that device current) with cudaGetSymbolAddress.
+// All calls share the array and it keeps the last call's contents: the hit-record region is cleared at the start
+// of each call, and two calls that overlap on one GPU (two contexts / threads on the same device) RACE.
+#define RT_STATIC_SCRATCH_BYTES ((size_t)RT_STATIC_MAX_RAYS * (sizeof(rt_ray) + sizeof(rt_hit)))
+static __device__ __align__(256) unsigned char g_static_scratch[RT_STATIC_SCRATCH_BYTES];
+
+// k_hits (rt_kernels.cuh) over the static array: rays at its start, hit records behind them
+__global__ void __launch_bounds__(128) k_hits_static(const __grid_constant__ DScene S, unsigned char* scratch, int n)
+{
+	const int k = blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	const rt_ray* rays = (const rt_ray*)scratch;
+	rt_hit* out = (rt_hit*)(scratch + (size_t)RT_STATIC_MAX_RAYS * sizeof(rt_ray));
+	const d3 o = ld3(rays[k].p), d = ld3(rays[k].d);
+	Hit h;
+	rt_hit r;
+	r.obj = r.face = -1;
+	r.N[0] = r.N[1] = r.N[2] = 0.0;
+	if (closest_hit<true>(S, o, d, h)) {
+		finalize_hit(S, o, d, h);
+		r.obj = h.obj;
+		r.face = h.face;
+		r.N[0] = h.N.x; r.N[1] = h.N.y; r.N[2] = h.N.z;
+	}
+	r.t = h.t;
+	out[k] = r;
+}
+
+rt_status rt_intersect_static(rt_ctx* ctx, const rt_ray* rays, int n, rt_hit* hits_out)
+{
+	if (!ctx) return RT_ERR_ARG;
+	if (!ctx->has_scene) { ctx->error = "no scene uploaded"; return RT_ERR_NO_SCENE; }
+	if (n < 0 || (n && (!rays || !hits_out))) { ctx->error = "bad arguments"; return RT_ERR_ARG; }
+	if (n > RT_STATIC_MAX_RAYS) {
+		ctx->error = "rt_intersect_static: n exceeds RT_STATIC_MAX_RAYS (" + std::to_string(RT_STATIC_MAX_RAYS) + " rays: the static device scratch is fixed-size; use rt_trace_rays)";
+		return RT_ERR_ARG;
+	}
+	if (n == 0) return RT_OK;
+	CK(cudaSetDevice(ctx->device));
+	if (!ctx->static_scratch) { // set-up, once per context: the symbol's address on THIS device
+		void* p = nullptr;
+		CK(cudaGetSymbolAddress(&p, g_static_scratch));
+		ctx->static_scratch = p;
+	}
+	unsigned char* scratch = (unsigned char*)ctx->static_scratch;
+	unsigned char* hits_dev = scratch + (size_t)RT_STATIC_MAX_RAYS * sizeof(rt_ray);
+	CK(cudaMemsetAsync(hits_dev, 0, (size_t)n * sizeof(rt_hit), ctx->stream)); // the array keeps the previous call's records
+	CK(cudaMemcpyAsync(scratch, rays, (size_t)n * sizeof(rt_ray), cudaMemcpyHostToDevice, ctx->stream));
+	k_hits_static<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(ctx->S, scratch, n);
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(hits_out, hits_dev, (size_t)n * sizeof(rt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return RT_OK;
+}
 
 rt_status rt_selftest_division(rt_ctx* ctx, long long n, unsigned long long seed, int exp_range, unsigned long long* mismatches)
 {

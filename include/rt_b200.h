@@ -134,6 +134,16 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int n, int depth,
                         rt_hit* hits_out, double* rgb_out);
 
+/* Scene::intersect for n <= RT_STATIC_MAX_RAYS rays with NO device allocation.  This entry point has no
+ * counterpart in the reference; it was added for callers that cannot
+ * call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  hits_out[n] is what
+ * rt_trace_rays(..., hits_out, NULL) returns.  The device staging of rays and hit records is a fixed file-scope
+ * device array (RT_STATIC_MAX_RAYS * 88 bytes = 352 KiB, held by every GPU that loads the library); the call
+ * makes no cudaMalloc / cudaFree.  n > RT_STATIC_MAX_RAYS is refused with RT_ERR_ARG.  All calls on a GPU share
+ * that array: calls that overlap on one GPU (two contexts or threads on the same device) race. */
+#define RT_STATIC_MAX_RAYS 4096
+rt_status rt_intersect_static(rt_ctx* ctx, const rt_ray* rays, int n, rt_hit* hits_out);
+
 /* Device self-test: n pseudo-random quotients a/d computed by the slab test's FMA-corrected
  * reciprocal division (device/rt_math.cuh div_by) are compared bit for bit with IEEE division;
  * exponents of a and d are drawn from [-exp_range, exp_range].  *mismatches must come back 0. */

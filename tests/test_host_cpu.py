@@ -334,3 +334,19 @@ def test_full_size_arena_hashes(rtlib, tmp_path, gen):
     data = arena.bytes()
     assert len(data) == want["arena_bytes"]
     assert hashlib.sha256(data).hexdigest() == want["arena_sha256"]
+
+
+def test_adapt_aa_known_answer(oracle_mod):
+    """/root/reference/adapt_aa.cpp, compiled unmodified by oracle/Makefile: its recursive
+    quadrant subdivision of a quarter disc on a 3000 x 3000 grid prints `area = 0.786317 (check= 0.785398)`.  It is a
+    different algorithm from RayTracer::adaptaa (that one is pinned by the frame tests), so this is a known-answer
+    check of the program itself: the estimate, and that it lies within 0.2 % of pi / 4."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "adapt_aa")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/adapt_aa not built")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120).stdout
+    m = re.match(r"area = ([0-9.]+) \(check= ([0-9.]+)\)", out)
+    assert m, out
+    area, check = float(m.group(1)), float(m.group(2))
+    assert out.strip() == "area = 0.786317 (check= 0.785398)"
+    assert abs(check - np.pi / 4) < 1e-6 and abs(area - check) < 2e-3

@@ -207,6 +207,63 @@ __device__ __forceinline__ void side_inv(RayInv& I, const d3& d, const ShadowSid
 	I.guard = (div_range_ok(d.x) && div_range_ok(d.y) && div_range_ok(d.z)) ? -1.0f : NAN;
 }
 
+// One (ray, candidate) pair of the shadow query, KIND known at compile time: the reference's own arithmetic - world
+// box pretest (scene.cpp:43), object-space ray (scene.cpp:17-20), intersectLocalList of that kind - and the
+// classification of its hits (classify_hit).  pos = global leaf item position (triangles only).
+template <int KIND>
+__device__ __forceinline__ unsigned cand_classify(const DScene& S, const d3& o, const d3& d, const ShadowSide& sd, unsigned obj, unsigned pos)
+{
+	const rt_object& ob = S.objs[obj];
+	RayInv I;
+	side_inv(I, d, sd);
+	double eb;
+	if (!box_hit(ob.bbox, ob.bbox + 3, o, d, I, eb)) return 0u; // scene.cpp:43
+	LocalRay L;
+	to_local(L, ob, o, d);
+	unsigned fl = 0;
+	if (KIND == RT_OBJ_TRIMESH) {
+		// TrimeshFace::intersectLocal and the isect it fills (trimesh.cpp:119-188), as emit_face
+		Hit h;
+		h.obj = (int)obj;
+		h.fpos = (int)pos;
+		h.face = S.mitems[pos];
+		h.uv.x = h.uv.y = 0.0;
+		double tl;
+		if (!tri_hit<true>(S.tris[pos], L.o, L.d, tl, h.bary)) return 0u;
+		const double t = tl / L.len;
+		if (!(t <= sd.limit)) return 0u;
+		const rt_mesh& M = S.meshes[ob.mesh];
+		const rt_face& fc = S.faces[M.face_off + h.face];
+		d3 Nl;
+		if (M.vnorm_off >= 0) {
+			const double* n0 = S.vnormals + 3 * (M.vnorm_off + fc.ids[0]);
+			const double* n1 = S.vnormals + 3 * (M.vnorm_off + fc.ids[1]);
+			const double* n2 = S.vnormals + 3 * (M.vnorm_off + fc.ids[2]);
+			Nl = normalize(mk3(n0[0] * h.bary.x + n1[0] * h.bary.y + n2[0] * h.bary.z,
+			                   n0[1] * h.bary.x + n1[1] * h.bary.y + n2[1] * h.bary.z,
+			                   n0[2] * h.bary.x + n1[2] * h.bary.y + n2[2] * h.bary.z));
+		} else {
+			Nl = ld3(fc.normal);
+		}
+		const d3 N = normalize(mul33(ob.normi, Nl));
+		d3 kt;
+		bool trans;
+		eval_kt(S, h, kt, trans);
+		fl = classify_hit(t, dot(N, d) > 0, trans, sd);
+	} else {
+		const ClassifyEmit emit{S, ob, d, L.len, sd, fl};
+		if (KIND == RT_OBJ_SPHERE) sphere_list(L.o, L.d, emit);
+		else if (KIND == RT_OBJ_BOX) box_list(L.o, L.d, emit);
+		else if (KIND == RT_OBJ_SQUARE) {
+			LocalHit lh;
+			lh.uv.x = lh.uv.y = 0.0;
+			if (square_hit<true>(L.o, L.d, lh)) emit(lh.t, lh.N, lh.uv, 0);
+		} else if (KIND == RT_OBJ_CYLINDER) cylinder_list(L.o, L.d, emit);
+		else cone_list(L.o, L.d, ob.cone, ob.capped, emit);
+	}
+	return fl;
+}
+
 #define RT_CAND_THREADS 128
 template <int KIND>
 __global__ void __launch_bounds__(RT_CAND_THREADS) k_shadow_cand(const __grid_constant__ DScene S, const RayQueue SQ, const ShadowSide* __restrict__ side, unsigned* flags,
@@ -228,54 +285,7 @@ __global__ void __launch_bounds__(RT_CAND_THREADS) k_shadow_cand(const __grid_co
 		if (__ldcg(flags + ray) & SH_DEAD) continue; // already settled by another candidate
 		const d3 o = SQ.load_v(0, ray), d = SQ.load_v(3, ray);
 		const ShadowSide sd = side[ray];
-		const rt_object& ob = S.objs[obj];
-		RayInv I;
-		side_inv(I, d, sd);
-		double eb;
-		if (!box_hit(ob.bbox, ob.bbox + 3, o, d, I, eb)) continue; // scene.cpp:43
-		LocalRay L;
-		to_local(L, ob, o, d);
-		unsigned fl = 0;
-		if (KIND == RT_OBJ_TRIMESH) {
-			// TrimeshFace::intersectLocal and the isect it fills (trimesh.cpp:119-188), as emit_face
-			Hit h;
-			h.obj = (int)obj;
-			h.fpos = (int)pos;
-			h.face = S.mitems[pos];
-			h.uv.x = h.uv.y = 0.0;
-			double tl;
-			if (!tri_hit<true>(S.tris[pos], L.o, L.d, tl, h.bary)) continue;
-			const double t = tl / L.len;
-			if (!(t <= sd.limit)) continue;
-			const rt_mesh& M = S.meshes[ob.mesh];
-			const rt_face& fc = S.faces[M.face_off + h.face];
-			d3 Nl;
-			if (M.vnorm_off >= 0) {
-				const double* n0 = S.vnormals + 3 * (M.vnorm_off + fc.ids[0]);
-				const double* n1 = S.vnormals + 3 * (M.vnorm_off + fc.ids[1]);
-				const double* n2 = S.vnormals + 3 * (M.vnorm_off + fc.ids[2]);
-				Nl = normalize(mk3(n0[0] * h.bary.x + n1[0] * h.bary.y + n2[0] * h.bary.z,
-				                   n0[1] * h.bary.x + n1[1] * h.bary.y + n2[1] * h.bary.z,
-				                   n0[2] * h.bary.x + n1[2] * h.bary.y + n2[2] * h.bary.z));
-			} else {
-				Nl = ld3(fc.normal);
-			}
-			const d3 N = normalize(mul33(ob.normi, Nl));
-			d3 kt;
-			bool trans;
-			eval_kt(S, h, kt, trans);
-			fl = classify_hit(t, dot(N, d) > 0, trans, sd);
-		} else {
-			const ClassifyEmit emit{S, ob, d, L.len, sd, fl};
-			if (KIND == RT_OBJ_SPHERE) sphere_list(L.o, L.d, emit);
-			else if (KIND == RT_OBJ_BOX) box_list(L.o, L.d, emit);
-			else if (KIND == RT_OBJ_SQUARE) {
-				LocalHit lh;
-				lh.uv.x = lh.uv.y = 0.0;
-				if (square_hit<true>(L.o, L.d, lh)) emit(lh.t, lh.N, lh.uv, 0);
-			} else if (KIND == RT_OBJ_CYLINDER) cylinder_list(L.o, L.d, emit);
-			else cone_list(L.o, L.d, ob.cone, ob.capped, emit);
-		}
+		const unsigned fl = cand_classify<KIND>(S, o, d, sd, obj, pos);
 		if (fl) atomicOr(flags + ray, fl);
 	}
 }

@@ -359,12 +359,47 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 #ifndef RT_SHADOW_MINB
 #define RT_SHADOW_MINB 16 // 64 registers, 16 blocks per SM (re-swept with wide rounds: profiles/r1_variants.txt)
 #endif
-__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt)
+// Sort key of a shadow ray: light (top bits) | 30-bit Morton code of the origin's cell in a 1024^3 grid over the scene's
+// box.  Rays of one light that start close together walk the same subtrees: sorted, the 32 rays of a warp stay
+// together in the node loop (the walk-length spread inside a warp is what leaves 7 of 32 lanes active) and their
+// node reads hit the same cache lines.
+__device__ __forceinline__ unsigned morton_spread10(unsigned v)
 {
-	const long long k = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
+	v &= 1023u;
+	v = (v | (v << 16)) & 0x030000ffu;
+	v = (v | (v << 8)) & 0x0300f00fu;
+	v = (v | (v << 4)) & 0x030c30c3u;
+	v = (v | (v << 2)) & 0x09249249u;
+	return v;
+}
+__global__ void __launch_bounds__(256) k_shadow_keys(const __grid_constant__ DScene S, const RayQueue SQ, long long n, unsigned* keys, unsigned* idx)
+{
+	const long long k = (long long)blockIdx.x * 256 + threadIdx.x;
+	if (k >= n) return;
+	const d3 o = SQ.load_v(0, k);
+	unsigned c[3];
+	const double oc[3] = {o.x, o.y, o.z};
+#pragma unroll
+	for (int a = 0; a < 3; a++) {
+		const double w = S.stree.hi[a] - S.stree.lo[a];
+		double f = w > 0.0 ? (oc[a] - S.stree.lo[a]) / w : 0.0;
+		f = f < 0.0 ? 0.0 : (f > 1.0 ? 1.0 : f);
+		c[a] = (unsigned)(f * 1023.0);
+	}
+	const unsigned m = morton_spread10(c[0]) | (morton_spread10(c[1]) << 1) | (morton_spread10(c[2]) << 2);
+	keys[k] = ((unsigned)SQ.i[SQ.cap + k] << 30) | m; // light index modulo 4 in the top two bits: a hint, not a requirement
+	idx[k] = (unsigned)k;
+}
+
+// perm: NULL, or the order in which the queue's rays are taken (k_shadow_keys + radix sort); n = rays in the queue
+__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt,
+                                                                                const unsigned* __restrict__ perm)
+{
+	const long long k0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
 	long long n = (long long)cnt->n_shadow[parity];
 	if (n > SQ.cap) n = SQ.cap;
-	if (k >= n) return;
+	if (k0 >= n) return;
+	const long long k = perm ? (long long)perm[k0] : k0;
 	const d3 ro = SQ.load_v(0, k), rd = SQ.load_v(3, k);
 	const rt_light& Lt = S.lights[SQ.i[SQ.cap + k]];
 	ShadowState st;

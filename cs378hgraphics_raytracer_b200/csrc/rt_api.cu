@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 #include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
 #include "rt_b200.h"
 #include "rt_arena_writer.hpp"
 #include "device/rt_kernels.cuh"
@@ -46,8 +47,11 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
-	bool shadow_split = false;             // RT_B200_SPLIT=1: the shadow stage as listing walk + per-kind candidate kernels (device/rt_scan.cuh).
-	                                       // Measured SLOWER than the one-kernel walk (profiles/r2_variants.txt: no any-hit exit in the listing walk), kept for A/B
+	bool sort_shadow = true;               // RT_B200_SORT=0: shadow rays are walked in queue order instead of (light, origin cell) order
+	int shadow_mode = 0;                   // how a round's shadow rays are walked (RT_B200_SHADOW=one|split|wb):
+	                                       //   0 one kernel, one thread per ray, candidates tested where they are met (k_wave_shadow)
+	                                       //   1 listing walk + per-kind candidate kernels (device/rt_scan.cuh): measured slower, kept for A/B
+	                                       //   2 one walk kernel with the candidates batched per warp and primitive kind (device/rt_shadow_wb.cuh)
 	bool kind_present[6] = {false, false, false, false, false, false}; // primitive kinds of the uploaded scene (a queue and a launch per kind present)
 	unsigned long long rounds = 0;
 	void* static_scratch = nullptr;        // device address of g_static_scratch on this context's GPU (rt_intersect_static)
@@ -63,8 +67,8 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
-       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_COUNT };
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
+       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -117,6 +121,7 @@ rt_status check_params(rt_ctx* ctx, const rt_params* p)
 	return RT_OK;
 }
 
+#define RT_SORT_MIN (1ll << 20) // rounds with fewer possible shadow rays are walked in queue order (a sort is ~20 us of launches)
 static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 rt_status make_queue(rt_ctx* ctx, int bd, int bi, long long cap, int nd, RayQueue& Q)
@@ -208,7 +213,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	long long W = ctx->wave_width;
 	if (W <= 0) {
 		// + per shadow ray of the split shadow stage: side record, flags, list entry and the candidate queues (launch_shadow_split)
-		const size_t per_ray = 4 * 104 + 2 * (size_t)(L > 0 ? L : 1) * 80 + 24 + (ctx->shadow_split ? (size_t)(L > 0 ? L : 1) * 200 : 0);
+		const size_t per_ray = 4 * 104 + 2 * (size_t)(L > 0 ? L : 1) * 80 + 24 + (ctx->shadow_mode == 1 ? (size_t)(L > 0 ? L : 1) * 200 : (ctx->shadow_mode == 2 ? (size_t)(L > 0 ? L : 1) * 4 : 0));
 		W = (long long)(ctx->queue_budget / per_ray) / 1024 * 1024;
 		// the spill stack (allocated only if a round ever has more than W children) may take another half of the memory
 		const long long spill_fit = (long long)(2 * ctx->queue_budget / (((size_t)(A.depth < 30 ? A.depth : 30) + 2) * 104)) / 1024 * 1024;
@@ -227,10 +232,20 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if ((st = make_queue(ctx, B_SQ2_D, B_SQ2_I, W * (L > 0 ? L : 1), 9, sq[1])) != RT_OK) return st;
 	// per-stage profiling wants clean kernel times: no overlap then
 	const bool overlap = ctx->overlap && !ctx->profile;
-	const bool split = ctx->shadow_split && L > 0;
+	const bool split = ctx->shadow_mode == 1 && L > 0;
+	const bool wb = ctx->shadow_mode == 2 && L > 0 && ctx->S.n_objs < (1 << 27); // the queues pack (object, owner lane) into 32 bits
 	CandQueues CQ;
 	std::memset(&CQ, 0, sizeof(CQ));
 	if (split && (st = make_cand_queues(ctx, W * L, CQ)) != RT_OK) return st;
+	unsigned kind_mask = 0;
+	if (wb) { // only the list of "complex" rays and its counter
+		if ((st = ensure(ctx, B_CQ_LIST, (size_t)W * L * sizeof(int))) != RT_OK) return st;
+		if ((st = ensure(ctx, B_CQ_CNT, 64)) != RT_OK) return st;
+		CQ.count = (unsigned long long*)ctx->buf[B_CQ_CNT];
+		CQ.n_complex = CQ.count + CQ_KINDS;
+		CQ.complex_list = (int*)ctx->buf[B_CQ_LIST];
+		for (int k = 0; k < CQ_KINDS; k++) kind_mask |= ctx->kind_present[k] ? 1u << k : 0u;
+	}
 	bool shadow_pending[2] = {false, false};
 	long long round = 0;
 	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
@@ -296,11 +311,41 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		shadow_pending[par] = false;
 		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
-		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry, shadow rays [2]
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
-		if (L > 0) {
+		// Large rounds: the shadow rays are walked in (light, origin cell) order.  The radix sort needs the number of rays on
+		// the host, which arrives with the counters the host waits for anyway - so the wait moves in front of the launch.
+		const bool sorted = L > 0 && !split && !wb && ctx->sort_shadow && m * L >= RT_SORT_MIN;
+		bool synced = false;
+		if (sorted) {
+			CK(cudaEventSynchronize(ctx->ev_round));
+			synced = true;
+			long long ns = (long long)ctx->pinned[4 + par];
+			if (ns > sq[par].cap) ns = sq[par].cap;
+			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
+			if (overlap) {
+				CK(cudaEventRecord(ctx->ev_shade[par], ctx->stream));
+				CK(cudaStreamWaitEvent(sstream, ctx->ev_shade[par], 0));
+			}
+			if (ns > 0) {
+				// sort buffers are per parity too (the other parity's walk may still be reading its permutation)
+				const int bk = par ? B_SK_B : B_SK_A, bi = par ? B_SI_B : B_SI_A;
+				if ((st = ensure(ctx, bk, (size_t)sq[par].cap * 2 * sizeof(unsigned))) != RT_OK) return st;
+				if ((st = ensure(ctx, bi, (size_t)sq[par].cap * 2 * sizeof(unsigned))) != RT_OK) return st;
+				unsigned* keys = (unsigned*)ctx->buf[bk];
+				unsigned* idx = (unsigned*)ctx->buf[bi];
+				size_t tmp_bytes = 0;
+				CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys + sq[par].cap, idx, idx + sq[par].cap, (int)ns, 0, 32, sstream));
+				const int bt = par ? B_CUBTMP2 : B_CUBTMP;
+				if ((st = ensure(ctx, bt, tmp_bytes)) != RT_OK) return st;
+				STAGE_ON(sstream, RT_STAGE_OTHER, k_shadow_keys<<<blocks_for(ns, 256), 256, 0, sstream>>>(ctx->S, sq[par], ns, keys, idx));
+				STAGE_ON(sstream, RT_STAGE_OTHER, CK(cub::DeviceRadixSort::SortPairs(ctx->buf[bt], tmp_bytes, keys, keys + sq[par].cap, idx, idx + sq[par].cap, (int)ns, 0, 32, sstream)));
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap));
+			}
+			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
+		} else if (L > 0) {
 			// the split stage's queues are shared by both parities: its pipelines follow one another on one stream
-			cudaStream_t sstream = overlap ? ctx->stream2[split ? 0 : par] : ctx->stream;
+			cudaStream_t sstream = overlap ? ctx->stream2[(split || wb) ? 0 : par] : ctx->stream;
 			if (overlap) {
 				CK(cudaEventRecord(ctx->ev_shade[par], ctx->stream));
 				CK(cudaStreamWaitEvent(sstream, ctx->ev_shade[par], 0));
@@ -308,12 +353,17 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
 			if (split) {
 				if ((st = launch_shadow_split(ctx, A, sq[par], par, cnt, m * L, CQ, sstream)) != RT_OK) return st;
+			} else if (wb) {
+				CK(cudaMemsetAsync(CQ.count, 0, 64, sstream));
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow_wb<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, CQ, kind_mask));
+				// the rays that met a transmissive / far-half surface (a few percent): the complete walk, persistent grid over the list
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow_list<<<(unsigned)ctx->sm_count * RT_SHADOW_MINB, RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], CQ));
 			} else
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt));
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr));
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
-		CK(cudaEventSynchronize(ctx->ev_round)); // the host plans the next round while the shadow rays run
+		if (!synced) CK(cudaEventSynchronize(ctx->ev_round)); // the host plans the next round while the shadow rays run
 		cur_n = (long long)ctx->pinned[0];
 		if (cur_n > nxt.cap) cur_n = nxt.cap; // overflow was flagged by the kernel
 		// the node budget follows the scene: if more than ~1.5 % of a round's rays ran out of it, the
@@ -328,7 +378,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		nxt = tmp;
 		ctx->rounds++;
 	}
-	if (split && getenv("RT_B200_DEBUG")) {
+	if ((split || wb) && getenv("RT_B200_DEBUG")) {
 		unsigned long long h[8];
 		cudaDeviceSynchronize();
 		cudaMemcpy(h, CQ.count, 64, cudaMemcpyDeviceToHost);
@@ -417,7 +467,8 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (cudaMallocHost((void**)&ctx->pinned, 64) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
 	if (const char* e = getenv("RT_B200_WAVE")) { const long long v = atoll(e); if (v >= 1024) ctx->wave_width = (v + 1023) / 1024 * 1024; }
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
-	if (const char* e = getenv("RT_B200_SPLIT")) ctx->shadow_split = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_SHADOW")) ctx->shadow_mode = !strcmp(e, "one") ? 0 : (!strcmp(e, "split") ? 1 : 2);
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;

@@ -126,11 +126,15 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 #ifndef RT_CLOSEST_MINB
 #define RT_CLOSEST_MINB 14 // 72 registers: the walk is latency bound, more resident warps beat fewer spills (profiles/r1_variants.txt)
 #endif
+// perm: NULL, or the order in which the first n_perm rays of the batch are taken (k_closest_keys + radix sort: reflection
+// and refraction rays arrive in the order their parents were shaded; sorted by direction octant and origin cell, the rays
+// of a warp walk the same subtrees).  Hit records stay indexed by queue slot, so the shade stage does not care.
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
-                                                                                    int budget, int* retry, unsigned long long* n_retry)
+                                                                                    int budget, int* retry, unsigned long long* n_retry, const unsigned* __restrict__ perm, long long n_perm)
 {
-	const long long k = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
-	if (k >= m) return;
+	const long long k0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
+	if (k0 >= m) return;
+	const long long k = k0 < n_perm ? (long long)perm[k0] : k0;
 	const long long q = base + k;
 	const int meta = Q.i[Q.cap + q];
 	if (((meta >> 12) & 15) == KIND_DEAD) return;
@@ -388,6 +392,27 @@ __global__ void __launch_bounds__(256) k_shadow_keys(const __grid_constant__ DSc
 	}
 	const unsigned m = morton_spread10(c[0]) | (morton_spread10(c[1]) << 1) | (morton_spread10(c[2]) << 2);
 	keys[k] = ((unsigned)SQ.i[SQ.cap + k] << 30) | m; // light index modulo 4 in the top two bits: a hint, not a requirement
+	idx[k] = (unsigned)k;
+}
+
+// sort key of a closest-hit ray: direction octant (3 bits) | 27-bit Morton code of the origin's cell (512^3 grid)
+__global__ void __launch_bounds__(256) k_closest_keys(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long n, unsigned* keys, unsigned* idx)
+{
+	const long long k = (long long)blockIdx.x * 256 + threadIdx.x;
+	if (k >= n) return;
+	const d3 o = Q.load_v(0, base + k), d = Q.load_v(3, base + k);
+	unsigned c[3];
+	const double oc[3] = {o.x, o.y, o.z};
+#pragma unroll
+	for (int a = 0; a < 3; a++) {
+		const double w = S.stree.hi[a] - S.stree.lo[a];
+		double f = w > 0.0 ? (oc[a] - S.stree.lo[a]) / w : 0.0;
+		f = f < 0.0 ? 0.0 : (f > 1.0 ? 1.0 : f);
+		c[a] = (unsigned)(f * 511.0);
+	}
+	const unsigned m = morton_spread10(c[0]) | (morton_spread10(c[1]) << 1) | (morton_spread10(c[2]) << 2);
+	const unsigned oct = (d.x < 0.0 ? 1u : 0u) | (d.y < 0.0 ? 2u : 0u) | (d.z < 0.0 ? 4u : 0u);
+	keys[k] = (oct << 27) | (m & 0x7ffffffu);
 	idx[k] = (unsigned)k;
 }
 

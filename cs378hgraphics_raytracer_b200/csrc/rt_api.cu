@@ -47,6 +47,7 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
+	bool sort_closest = true;              // RT_B200_SORTC=0: reflection / refraction rays are walked in queue order instead of (octant, origin cell) order
 	bool sort_shadow = true;               // RT_B200_SORT=0: shadow rays are walked in queue order instead of (light, origin cell) order
 	int shadow_mode = 0;                   // how a round's shadow rays are walked (RT_B200_SHADOW=one|split|wb):
 	                                       //   0 one kernel, one thread per ray, candidates tested where they are met (k_wave_shadow)
@@ -67,8 +68,8 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
-       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_COUNT };
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
+       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -262,6 +263,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	long long cur_n = 0, sp_n = 0, cam = 0;
 	for (;;) {
 		long long base = 0, m = 0;
+		long long n_kids = cur_n < W ? cur_n : W; // the batch's first n_kids rays are children of the previous round
 		if (cur_n > W) {
 			// more children than one round takes: the oldest go to the spill stack
 			const long long spill = cur_n - W;
@@ -296,8 +298,21 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
 		// a forced budget (RT_B200_BUDGET, the tests) sends its leftovers straight to the cooperative kernel
 		const bool second = ctx->budget_auto && ctx->walk_budget > 0;
+		const unsigned* cperm = nullptr;
+		if (ctx->sort_closest && n_kids >= RT_SORT_MIN) {
+			if ((st = ensure(ctx, B_CK, (size_t)W * 2 * sizeof(unsigned))) != RT_OK) return st;
+			if ((st = ensure(ctx, B_CI, (size_t)W * 2 * sizeof(unsigned))) != RT_OK) return st;
+			unsigned* keys = (unsigned*)ctx->buf[B_CK];
+			unsigned* idx = (unsigned*)ctx->buf[B_CI];
+			size_t tmp_bytes = 0;
+			CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys + W, idx, idx + W, (int)n_kids, 0, 30, ctx->stream));
+			if ((st = ensure(ctx, B_CUBTMP3, tmp_bytes)) != RT_OK) return st;
+			STAGE(RT_STAGE_OTHER, k_closest_keys<<<blocks_for(n_kids, 256), 256, 0, ctx->stream>>>(ctx->S, cur, base, n_kids, keys, idx));
+			STAGE(RT_STAGE_OTHER, CK(cub::DeviceRadixSort::SortPairs(ctx->buf[B_CUBTMP3], tmp_bytes, keys, keys + W, idx, idx + W, (int)n_kids, 0, 30, ctx->stream)));
+			cperm = idx + W;
+		} else n_kids = 0;
 		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget,
-		                                                                                                                second ? retry : heavy, second ? &cnt->n_retry : &cnt->n_heavy));
+		                                                                                                                second ? retry : heavy, second ? &cnt->n_retry : &cnt->n_heavy, cperm, n_kids));
 		if (second) {
 			// second chance with 8 x the budget: grid for 1/32 of the round (a grid-stride loop takes whatever there is)
 			const unsigned rblocks = blocks_for((m + 31) / 32, RT_TRACE_THREADS);
@@ -468,6 +483,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_WAVE")) { const long long v = atoll(e); if (v >= 1024) ctx->wave_width = (v + 1023) / 1024 * 1024; }
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SHADOW")) ctx->shadow_mode = !strcmp(e, "one") ? 0 : (!strcmp(e, "split") ? 1 : 2);
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs

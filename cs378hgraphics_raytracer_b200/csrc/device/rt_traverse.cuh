@@ -403,8 +403,8 @@ template <int FIXED_MODE> RT_COLD void walk_mesh_exit(const DScene& S, Walk& W, 
 }
 
 // FIXED_MODE >= 0 compiles the walk for one query kind only (the wavefront's stage kernels).
-// budget > 0: give up after that many stack pops (subtrees) and return false - the caller hands the ray
-// to the warp-cooperative walk (rt_coop.cuh).  A few rays visit thousands of nodes (a zero direction
+// budget > 0: give up once that many tree nodes have been visited (noticed at the next stack pop) and return false - the
+// caller hands the ray to the warp-cooperative walk (rt_coop.cuh).  A few rays visit thousands of nodes (a zero direction
 // component makes the reference's slab test accept every box along that axis, bbox.cc:43) and a
 // warp waits for its slowest lane; the result of an abandoned walk is not used.
 // All ways out of the loop are in the pop section: a second exit inside the node or leaf loops costs
@@ -431,12 +431,14 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 	int cur = walk_begin(S, W, F, limf);
 	if (cur == RT_REF_NONE) return true;
 	bool done = true;
+	const bool limited = budget > 0;
 	for (;;) {
 		// ---- 1. internal nodes: test both children, go near, push far ---------------------------
 #pragma unroll 1
 		while (cur >= 0) {
 			const DNode2f nf = ld_node2f(nodesf + cur);
 			RT_CNT(nodes, mode);
+			budget--;
 			float e0, e1;
 			int r0 = boxf(nf.lo0, nf.hi0, F, e0);
 			int r1 = boxf(nf.lo1, nf.hi1, F, e1);
@@ -475,7 +477,7 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 #pragma unroll 1
 			for (;;) {
 				if (sp == 0) break;
-				if (--budget == 0) { done = false; break; }
+				if (limited && budget <= 0) { done = false; break; }
 				sp--;
 				const StackEnt a = stk[sp];
 				if (a.ref == RT_REF_MESH_EXIT) {

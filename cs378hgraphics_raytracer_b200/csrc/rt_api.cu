@@ -37,7 +37,7 @@ struct rt_ctx {
 	// wavefront path
 	long long wave_width = 0;              // rays per round; 0 = chosen per call from the memory budget below (RT_B200_WAVE overrides)
 	size_t queue_budget = 0;               // bytes the ray queues of a round may take: a quarter of the device memory
-	int walk_budget = 40;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
+	int walk_budget = 96;                  // tree nodes a single thread spends on one ray before the warp-cooperative walk takes it (RT_B200_BUDGET; 0 = never)
 	int n_area_lights = 0;                 // area + spot lights of the uploaded scene
 	bool budget_auto = true;               // no RT_B200_BUDGET given: the budget adapts to the scene
 	bool use_pool = false;                 // RT_B200_POOL=1: the fused persistent kernel instead
@@ -673,7 +673,7 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	CK(cudaStreamSynchronize(ctx->stream)); // also: the caller may reuse `arena` on return
 	if (hflags[0]) { ctx->error = "invalid arena: index out of range (device check " + std::to_string(hflags[0]) + ")"; return RT_ERR_ARG; }
 	if ((hflags[1] | hflags[2]) & 0x80000000u || hflags[1] + hflags[2] > RT_STACK - 4) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
-	if (ctx->budget_auto) ctx->walk_budget = 40;
+	if (ctx->budget_auto) ctx->walk_budget = 96;
 	ctx->n_area_lights = n_area;
 	ctx->has_scene = true;
 	return RT_OK;

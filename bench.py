@@ -224,6 +224,19 @@ def run_reference(args, wl, rank):
            "config": {"workload": wl["name"], "width": w, "height": h, "scene": "procedural stand-in (scenes/gen_scenes.py)"},
            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": desc + " per step"},
            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    # the dragon frame (targets.c3 of the b200 arm): the whole frame, it takes the host cores about a second
+    out["targets"] = {}
+    for tkey in [t for t in args.targets.split(",") if t and t != args.workload]:
+        twl = WORKLOADS[tkey]
+        torc = ob.Oracle(None, arena=load_arena(twl))
+        tp = rt.Params.default(**twl["params"])
+        tw = twl["w"]
+        th = ob.frame_height(tw, torc.aspect)
+        full = tkey in ("c1", "c2", "c3")
+        r, s, desc = reference_sample(torc, tp, tw, th, 1e9 if full else budget)
+        out["targets"][tkey] = {"value": r / s / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * s, "cores": cores, "sample": desc,
+                                "config": {"workload": twl["name"], "width": tw, "height": th},
+                                "e2e": {"value": r / s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out), flush=True)
 
 
@@ -255,18 +268,11 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def run_b200(args, key, wl, rank, world, local_rank):
+def measure(S, key, wl, steps, warmup, cpu_seconds, cpu_full_frame):
+    """One workload on the session's GPUs: the bench line's fields for it (rank 0 returns the dict, the others None).
+    S = session (ctx, rank, world, device, dist, modules)."""
     import torch
-    import torch.distributed as dist
-    import cs378hgraphics_raytracer_b200 as rt
-    from cs378hgraphics_raytracer_b200 import parallel as par
-    import oracle_binding as ob
-
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=device)
-    ctx = rt.Context(local_rank)
+    rt, par, ob, ctx, rank, world, device, dist = S["rt"], S["par"], S["ob"], S["ctx"], S["rank"], S["world"], S["device"], S["dist"]
     params = rt.Params.default(**wl["params"])
 
     # scene: rank 0 parses + flattens, NCCL broadcast replicates it (north star: scene replicated)
@@ -286,12 +292,10 @@ def run_b200(args, key, wl, rank, world, local_rank):
     upload()
     hdr = np.frombuffer(arena_bytes[:32 + 17 * 24], dtype=np.uint64)
     cam = np.frombuffer(arena_bytes[int(hdr[4 + 3 * 1 + 1]):int(hdr[4 + 3 * 1 + 1]) + 14 * 8], dtype=np.float64)
-    cam_aspect = float(cam[12])
     w = wl["w"]
-    h = ob.frame_height(w, cam_aspect)
-    n_items = int(hdr[4 + 3 * 12 + 2])
+    h = ob.frame_height(w, float(cam[12]))
     h2d_bytes = len(arena_bytes)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+    flush = S["flush"]
 
     def barrier():
         if world > 1:
@@ -302,13 +306,15 @@ def run_b200(args, key, wl, rank, world, local_rank):
         flush.fill_(1)
         torch.cuda.synchronize()
         ptr, st = ctx.render_device(params, w, h, rank, world)
-        full = None
         if world > 1:
-            full = par.gather_frame(par.device_frame(ptr, w, h, device), rank, world)
+            par.gather_frame(par.device_frame(ptr, w, h, device), rank, world)
             torch.cuda.synchronize()
-        return st, full
+        return st
 
-    def step_e2e(host_out):
+    host_pinned = torch.empty((h, w, 3), dtype=torch.uint8, pin_memory=True)  # the caller's frame buffer, page-locked
+    host_out = host_pinned.numpy()
+
+    def step_e2e():
         upload()
         if world == 1:
             _, st = ctx.render(params, w, h, out=host_out)
@@ -320,18 +326,19 @@ def run_b200(args, key, wl, rank, world, local_rank):
             torch.cuda.synchronize()
         return st
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step_resident()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(S["local_rank"])
     if rank == 0:
         sampler.start()
     barrier()
     t0 = time.perf_counter()
-    rays = launches = 0
+    rays = launches = culled = 0
     dev_ms = 0.0
-    for _ in range(args.steps):
-        st, _ = step_resident()
+    for _ in range(steps):
+        st = step_resident()
         rays += st.rays
+        culled += st.culled_shadow_rays
         launches += st.launches
         dev_ms += st.device_ms
     barrier()
@@ -340,106 +347,145 @@ def run_b200(args, key, wl, rank, world, local_rank):
     # the L2 flush is not part of the step: measure it alone and take it out
     torch.cuda.synchronize()
     f0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         flush.fill_(1)
         torch.cuda.synchronize()
     flush_s = time.perf_counter() - f0
     elapsed = max(1e-9, (t1 - t0) - flush_s)
 
-    host_pinned = torch.empty((h, w, 3), dtype=torch.uint8, pin_memory=True)  # the caller's frame buffer, page-locked
-    host_out = host_pinned.numpy()
-    step_e2e(host_out)
+    step_e2e()
     barrier()
     e0 = time.perf_counter()
     e_rays = 0
-    for _ in range(args.steps):
-        e_rays += step_e2e(host_out).rays
+    for _ in range(steps):
+        e_rays += step_e2e().rays
     barrier()
     e1 = time.perf_counter()
-
     # per-stage device times: the same frames once more with CUDA events around every launch
     # (rt_set_profiling); kept out of the timed region above because the extra events cost a few
-    # microseconds per launch
+    # microseconds per launch and the stages are serialised for clean times
     ctx.set_profiling(True)
     stage_ms = np.zeros(6)
     stage_n = np.zeros(6)
     kind_rays = np.zeros(2)
-    culled = 0
-    for _ in range(args.steps):
-        st, _ = step_resident()
+    for _ in range(steps):
+        st = step_resident()
         stage_ms += np.array(list(st.stage_ms))
         stage_n += np.array(list(st.stage_launches))
         # rays the two walk kernels really walked: shadow rays dropped by k_wave_shade (exactly zero Phong term) are not among them
         kind_rays += np.array([st.camera_rays + st.reflection_rays + st.refraction_rays, st.shadow_rays - st.culled_shadow_rays], dtype=np.float64)
-        culled += st.culled_shadow_rays
     ctx.set_profiling(False)
 
-    stats = torch.tensor([float(rays), float(e_rays), float(launches), elapsed, e1 - e0, dev_ms], dtype=torch.float64, device=device)
+    stats = torch.tensor([float(rays), float(e_rays), float(launches), elapsed, e1 - e0, dev_ms, float(culled)], dtype=torch.float64, device=device)
     if world > 1:
-        sums = stats.clone()
+        sums, maxs, mins = stats.clone(), stats.clone(), stats.clone()
         dist.all_reduce(sums, op=dist.ReduceOp.SUM)
-        maxs = stats.clone()
         dist.all_reduce(maxs, op=dist.ReduceOp.MAX)
+        dist.all_reduce(mins, op=dist.ReduceOp.MIN)
     else:
-        sums = maxs = stats
+        sums = maxs = mins = stats
+    if rank != 0:
+        return None
+    tot_rays, tot_e_rays, tot_launches, tot_culled = float(sums[0]), float(sums[1]), int(sums[2]), float(sums[6])
+    t_max, e_max, dev_ms_max, dev_ms_min = float(maxs[3]), float(maxs[4]), float(maxs[5]), float(mins[5])
+    value = tot_rays / t_max / 1e6
+    out = {"metric": "Mrays/s (primary+secondary+shadow)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": steps,
+           "warmup": warmup, "ms_per_step": 1e3 * t_max / steps, "higher_is_better": True, "scaling": "strong",
+           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           # `config` is the same object on both arms (--impl reference); what depends on the run is in config_notes
+           "config": {"workload": wl["name"], "width": w, "height": h, "scene": "procedural stand-in (scenes/gen_scenes.py)"},
+           "config_notes": {"rays_per_frame": tot_rays / steps, "scene": "the reference's own asset is not in its repository (SURVEY.md 0.3)",
+                      "partition": "interleaved 32x32 tiles, tile t -> rank t %% %d; scene replicated" % world,
+                      "l2": "256 MiB L2 flush between timed frames (its own time subtracted)",
+                      "rays": "counted as the instrumented reference counts them; %d shadow rays per frame are counted but not walked (Phong term exactly 0: their contribution is 0 whatever they hit) - value_walked leaves them out" % (tot_culled // max(1, steps))},
+           # the same throughput over the rays the GPU really walks (what the roofline below is about)
+           "value_walked": (tot_rays - tot_culled) / t_max / 1e6,
+           # CUDA events on the launching stream around each frame's device work; max and min over ranks tell tile imbalance
+           # (max >> min) from round tails (both far above the N = 1 time / N); the gather is outside them
+           "device_ms_per_step": dev_ms_max / steps, "device_ms_per_step_min_rank": dev_ms_min / steps,
+           "clocks": clocks, "gpu_launches": tot_launches,
+           "e2e": {"value": tot_e_rays / e_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": w * h * 3,
+                   "what": "rt_upload_scene (whole scene arena, pinned host -> device, layouts rebuilt on the device) + render + RGB8 frame device -> host, every step"}}
+    # roofline of the dominant kernel (rank 0's stage times)
+    cm = load_cost_model(key)
+    peak, peak_src = measured_peaks()
+    fp64_peak, fp32_peak = ctx.measure_fma_peak()
+    names = rt.Stats.STAGES
+    out["stages"] = {names[k]: {"ms_per_step": stage_ms[k] / steps, "launches_per_step": stage_n[k] / steps} for k in range(6) if stage_n[k] > 0}
+    if cm and stage_ms.sum() > 0:
+        closest_ms, shadow_ms = stage_ms[1] + stage_ms[2], stage_ms[4]
+        kind, kernel, k_ms, k_n = ("shadow", "k_wave_shadow", shadow_ms, stage_n[4]) if shadow_ms >= closest_ms else \
+                                  ("closest", "k_wave_closest (+ k_wave_closest_heavy)", closest_ms, stage_n[1])
+        ck = cm["kinds"][kind]
+        n_rays = kind_rays[0 if kind == "closest" else 1]
+        alg_bytes = ck["bytes_per_ray"] * n_rays
+        ach = alg_bytes / (k_ms * 1e-3) / 1e9
+        # bytes of the records the kernel really reads for the same visits: 64 B float node (both children), 32 B float item
+        # box, 96 B triangle, 248 B object (inverse, normal matrix, box) + 96 B ray in / result out
+        lay_bytes = (64.0 * ck["nodes_per_ray"] + 32.0 * ck["objs_per_ray"] + 96.0 * ck["tris_per_ray"] + 248.0 * min(ck["objs_per_ray"], 3.0) + 96.0) * n_rays
+        # DRAM bytes and counters of this kernel from the committed ncu capture of one launch
+        tr = load_dram_traffic(key, kind)
+        traffic, traffic_src, cnt = None, None, {}
+        if isinstance(tr, dict) and tr.get("launch_ms"):
+            traffic = tr["bytes"] * (k_ms / max(k_n, 1)) / tr["launch_ms"]
+            traffic_src = "%s; scaled from its %.2f ms to this run's %.2f ms per launch" % (tr.get("source", ""), tr["launch_ms"], k_ms / max(k_n, 1))
+            cnt = tr.get("counters", {})
+        fp64_ach = ck["flops_per_ray"] * n_rays / (k_ms * 1e-3) / 1e12
+        out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                           "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": kernel,
+                           "kernel_ms_per_launch": k_ms / max(k_n, 1), "launches_per_step": k_n / steps,
+                           "algorithmic_bytes_per_launch": alg_bytes / max(k_n, 1), "bytes_per_ray": ck["bytes_per_ray"],
+                           "numerator": "SURVEY 8(d) formula (64 B per box, 128 B per triangle, 192 B per object, 96 B per ray) over the DEVICE walk's own visit "
+                                        "counts (host build of the device headers with counters, scenes/cost_model.py) - not an oracle-derived lower bound",
+                           "kernel_layout_bytes_per_launch": lay_bytes / max(k_n, 1), "kernel_layout_frac": lay_bytes / (k_ms * 1e-3) / 1e9 / peak,
+                           # what the counters say (ncu capture of one launch of this kernel, profiles/): none of the three roofs is near
+                           "dram_frac": (traffic / (k_ms / max(k_n, 1) * 1e-3) / 1e9 / peak) if traffic else None,
+                           "fp64_frac": fp64_ach / fp64_peak if fp64_peak else None,
+                           "lanes_per_inst": cnt.get("lanes_per_inst"), "issue_active_pct": cnt.get("issue_active_pct"),
+                           "limiter": "latency and divergence: the scene is cache resident, DRAM and FP64 are idle; the walk is a chain of dependent L2 accesses at a fraction of the 32 lanes (DESIGN.md section 5)",
+                           "fp64": {"flops_per_ray": ck["flops_per_ray"], "achieved_tflops": fp64_ach, "peak_tflops": fp64_peak,
+                                    "peak_source": "measured: rt_measure_fma_peak (8 FMA chains per thread)", "fp32_peak_tflops": fp32_peak}}
+    else:
+        out["roofline"] = None
+    # the reference on this box's host cores (N = 1 only): a bounded sample, or the whole frame where that takes seconds
+    if world == 1 and ob.available() and cpu_seconds > 0:
+        arena = load_arena(wl)
+        orc = ob.Oracle(None, arena=arena)
+        r, s, desc = reference_sample(orc, params, w, h, 1e9 if cpu_full_frame else cpu_seconds)
+        out["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": ob.ref().ref_get_threads(), "kind": "reference", "sample": desc}
+    else:
+        out["cpu_baseline"] = None
+    return out
+
+
+def run_b200(args, key, wl, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import cs378hgraphics_raytracer_b200 as rt
+    from cs378hgraphics_raytracer_b200 import parallel as par
+    import oracle_binding as ob
+
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    S = {"rt": rt, "par": par, "ob": ob, "ctx": rt.Context(local_rank), "rank": rank, "world": world, "device": device, "dist": dist,
+         "local_rank": local_rank, "flush": torch.empty(256 << 20, dtype=torch.uint8, device=device)}  # flush buffer > 126 MB L2
+    cpu_s = 0.0 if args.no_cpu_baseline else args.cpu_seconds
+    out = measure(S, key, wl, args.steps, args.warmup, cpu_s, False)
+    # the scene the north star's target names (the dragon, C3), measured in the same run and - under torchrun - at the same N,
+    # so that the driver's BENCH / SCALE records carry it next to the headline workload
+    targets = {}
+    for tkey in [t for t in args.targets.split(",") if t and t != key]:
+        twl = WORKLOADS[tkey]
+        t = measure(S, tkey, twl, max(5, args.steps), max(3, args.warmup), cpu_s, tkey in ("c1", "c2", "c3"))
+        if t is not None:
+            targets[tkey] = {k: t[k] for k in ("value", "value_walked", "unit", "ms_per_step", "device_ms_per_step", "device_ms_per_step_min_rank", "steps", "warmup",
+                                               "gpu_launches", "e2e", "roofline", "cpu_baseline", "stages", "config", "config_notes")}
     if rank == 0:
-        tot_rays, tot_e_rays, tot_launches = float(sums[0]), float(sums[1]), int(sums[2])
-        t_max, e_max, dev_ms_max = float(maxs[3]), float(maxs[4]), float(maxs[5])
-        value = tot_rays / t_max / 1e6
-        out = {"metric": "Mrays/s (primary+secondary+shadow)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
-               "warmup": args.warmup, "ms_per_step": 1e3 * t_max / args.steps, "higher_is_better": True, "scaling": "strong",
-               "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-               "config": {"workload": wl["name"], "width": w, "height": h, "rays_per_frame": tot_rays / args.steps,
-                          "scene": "procedural stand-in (scenes/gen_scenes.py); real asset not in the reference repo",
-                          "partition": "interleaved 32x32 tiles, tile t -> rank t %% %d; scene replicated" % world,
-                          "l2": "256 MiB L2 flush between timed frames (its own time subtracted)",
-                          "rays": "counted as the instrumented reference counts them; %d shadow rays per frame on this rank are counted but not walked (Phong term exactly 0: their contribution is 0 whatever they hit)" % (culled // max(1, args.steps))},
-               "device_ms_per_step": dev_ms_max / args.steps,  # CUDA events on the launching stream around each frame's device work (max over ranks); the gather is outside them
-               "clocks": clocks, "gpu_launches": tot_launches,
-               "e2e": {"value": tot_e_rays / e_max / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": w * h * 3,
-                       "what": "rt_upload_scene (whole scene arena, pinned host -> device, layouts rebuilt on the device) + render + RGB8 frame device -> host, every step"}}
-        # roofline of the dominant kernel (rank 0's stage times): algorithmic bytes of the rays that
-        # kernel walked (scenes/cost_model.json, per ray kind) / its device time
-        cm = load_cost_model(key)
-        peak, peak_src = measured_peaks()
-        fp64_peak, fp32_peak = ctx.measure_fma_peak()
-        names = rt.Stats.STAGES
-        out["stages"] = {names[k]: {"ms_per_step": stage_ms[k] / args.steps, "launches_per_step": stage_n[k] / args.steps} for k in range(6) if stage_n[k] > 0}
-        if cm and stage_ms.sum() > 0:
-            closest_ms, shadow_ms = stage_ms[1] + stage_ms[2], stage_ms[4]
-            kind, kernel, k_ms, k_n = ("shadow", "k_wave_shadow", shadow_ms, stage_n[4]) if shadow_ms >= closest_ms else \
-                                      ("closest", "k_wave_closest (+ k_wave_closest_heavy)", closest_ms, stage_n[1])
-            ck = cm["kinds"][kind]
-            n_rays = kind_rays[0 if kind == "closest" else 1]
-            alg_bytes = ck["bytes_per_ray"] * n_rays
-            ach = alg_bytes / (k_ms * 1e-3) / 1e9
-            # DRAM bytes of this kernel's average launch, from the committed ncu capture of one launch scaled by duration
-            tr = load_dram_traffic(key, kind)
-            traffic, traffic_src = None, None
-            if isinstance(tr, dict) and tr.get("launch_ms"):
-                traffic = tr["bytes"] * (k_ms / max(k_n, 1)) / tr["launch_ms"]
-                traffic_src = "%s; scaled from its %.2f ms to this run's %.2f ms per launch" % (tr.get("source", ""), tr["launch_ms"], k_ms / max(k_n, 1))
-            out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                               "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": kernel,
-                               "kernel_ms_per_launch": k_ms / max(k_n, 1), "launches_per_step": k_n / args.steps,
-                               "algorithmic_bytes_per_launch": alg_bytes / max(k_n, 1), "bytes_per_ray": ck["bytes_per_ray"],
-                               "note": "the walk is FP64-latency bound, not bandwidth bound: the scene is L2 resident (DESIGN.md, roofline)",
-                               "fp64": {"flops_per_ray": ck["flops_per_ray"], "achieved_tflops": ck["flops_per_ray"] * n_rays / (k_ms * 1e-3) / 1e12,
-                                        "peak_tflops": fp64_peak,
-                                        "peak_source": "measured: rt_measure_fma_peak (8 FMA chains per thread)", "fp32_peak_tflops": fp32_peak}}
-        else:
-            out["roofline"] = None
-        # the reference on this box's host cores, bounded sample (N = 1 only)
-        if world == 1 and ob.available() and not args.no_cpu_baseline:
-            arena = load_arena(wl)
-            orc = ob.Oracle(None, arena=arena)
-            r, s, desc = reference_sample(orc, params, w, h, args.cpu_seconds)
-            out["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": ob.ref().ref_get_threads(), "kind": "reference",
-                                   "sample": desc}
-        else:
-            out["cpu_baseline"] = None
+        out["targets"] = targets
         print(json.dumps(out), flush=True)
-    ctx.close()
+    S["ctx"].close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -455,6 +501,7 @@ def main():
     ap.add_argument("--workload", default="c5", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="host-core time spent on the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--targets", default="c3", help="comma list of further workloads measured in the same run and reported under `targets` (the dragon scene the north star's ratio names); '' = none")
     args = ap.parse_args()
     # stdout carries ONE JSON line and nothing else: libraries that write to file descriptor 1 (NCCL prints
     # "NCCL version ..." there when NCCL_DEBUG is set) are sent to stderr, the line goes to the saved descriptor

@@ -307,7 +307,7 @@ def measure(S, key, wl, steps, warmup, cpu_seconds, cpu_full_frame):
         torch.cuda.synchronize()
         ptr, st = ctx.render_device(params, w, h, rank, world)
         if world > 1:
-            par.gather_frame(par.device_frame(ptr, w, h, device), rank, world)
+            par.gather_frame_device(ctx, ptr, w, h, rank, world, device)
             torch.cuda.synchronize()
         return st
 
@@ -320,7 +320,7 @@ def measure(S, key, wl, steps, warmup, cpu_seconds, cpu_full_frame):
             _, st = ctx.render(params, w, h, out=host_out)
         else:
             ptr, st = ctx.render_device(params, w, h, rank, world)
-            full = par.gather_frame(par.device_frame(ptr, w, h, device), rank, world)
+            full = par.gather_frame_device(ctx, ptr, w, h, rank, world, device)
             if rank == 0:
                 host_pinned.copy_(full, non_blocking=True)  # page-locked destination: one DMA, no staging copy
             torch.cuda.synchronize()

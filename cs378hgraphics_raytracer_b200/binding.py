@@ -93,6 +93,10 @@ def lib():
                                    ctypes.POINTER(vp), ctypes.POINTER(Stats)]
     L.rt_trace_pixels.argtypes = [vp, ctypes.POINTER(Params), ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, vp]
     L.rt_trace_rays.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, ctypes.c_int, vp, vp]
+    L.rt_pack_tiles.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp]
+    L.rt_pack_tiles.restype = i32
+    L.rt_unpack_tiles.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, vp]
+    L.rt_unpack_tiles.restype = i32
     L.rt_intersect_static.argtypes = [vp, vp, ctypes.c_int, vp]
     L.rt_intersect_static.restype = i32
     L.rt_selftest_division.argtypes = [vp, ctypes.c_longlong, ctypes.c_ulonglong, ctypes.c_int, ctypes.POINTER(ctypes.c_ulonglong)]
@@ -283,6 +287,13 @@ class Context:
         out = np.zeros((len(ij), 3))
         self._check(lib().rt_trace_pixels(self._h, ctypes.byref(params), w, h, ij.ctypes.data, len(ij), out.ctypes.data))
         return out
+
+    def pack_tiles(self, dev_rgb, w, h, part, n_parts, dev_packed):
+        """rt_pack_tiles: this partition's tiles of the device frame -> contiguous device block (device pointers as ints)."""
+        self._check(lib().rt_pack_tiles(self._h, ctypes.c_void_p(dev_rgb), w, h, part, n_parts, ctypes.c_void_p(dev_packed)))
+
+    def unpack_tiles(self, dev_gathered, w, h, n_parts, tiles_cap, dev_rgb_out):
+        self._check(lib().rt_unpack_tiles(self._h, ctypes.c_void_p(dev_gathered), w, h, n_parts, tiles_cap, ctypes.c_void_p(dev_rgb_out)))
 
     def intersect_static(self, rays):
         """rt_intersect_static: Scene::intersect for at most STATIC_MAX_RAYS rays, no device allocation."""

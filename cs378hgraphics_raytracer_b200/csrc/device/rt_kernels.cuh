@@ -240,6 +240,36 @@ __global__ void __launch_bounds__(256) k_adapt_store(const PoolArgs A, long long
 } // namespace rtd
 
 namespace rtd {
+// ---- framebuffer gather of the tile partition ----------------------------------------------------
+// A rank's tiles (t = part, part + n_parts, ...) as one contiguous block, 32 x 32 x 3 bytes per tile in tile order: what is
+// sent to the gathering rank instead of the whole frame.  Pixels of an edge tile outside the image are 0.
+__global__ void __launch_bounds__(256) k_pack_tiles(const uint8_t* __restrict__ fb, int w, int h, int tiles_x, int part, int n_parts, long long n_local, uint8_t* __restrict__ packed)
+{
+	const long long p = (long long)blockIdx.x * 256 + threadIdx.x; // local pixel
+	if (p >= n_local * RT_TILE_PIX) return;
+	const long long tile = (p / RT_TILE_PIX) * n_parts + part;
+	const int q = (int)(p % RT_TILE_PIX);
+	const int x = (int)(tile % tiles_x) * RT_TILE + (q & 31), y = (int)(tile / tiles_x) * RT_TILE + (q >> 5);
+	uint8_t r = 0, g = 0, b = 0;
+	if (x < w && y < h) {
+		const uint8_t* px = fb + ((size_t)y * w + x) * 3;
+		r = px[0]; g = px[1]; b = px[2];
+	}
+	packed[3 * p] = r; packed[3 * p + 1] = g; packed[3 * p + 2] = b;
+}
+// The gathering rank's inverse: gathered = n_parts blocks of tiles_cap packed tiles (rank r's block holds its tiles in order).
+__global__ void __launch_bounds__(256) k_unpack_tiles(const uint8_t* __restrict__ gathered, int w, int h, int tiles_x, int n_parts, long long tiles_cap, uint8_t* __restrict__ fb)
+{
+	const long long p = (long long)blockIdx.x * 256 + threadIdx.x; // pixel of the frame
+	if (p >= (long long)w * h) return;
+	const int x = (int)(p % w), y = (int)(p / w);
+	const long long tile = (long long)(y / RT_TILE) * tiles_x + x / RT_TILE;
+	const long long rank = tile % n_parts, lt = tile / n_parts;
+	const uint8_t* src = gathered + ((rank * tiles_cap + lt) * RT_TILE_PIX + (y % RT_TILE) * RT_TILE + x % RT_TILE) * 3;
+	uint8_t* px = fb + (size_t)p * 3;
+	px[0] = src[0]; px[1] = src[1]; px[2] = src[2];
+}
+
 // RayTracer::tracePixel's return value for explicit samples (clamped mean over lens rays,
 // anaglyph red from the second eye)
 __global__ void __launch_bounds__(256) k_sample_values(const double* accum, const double* accum2, long long n, rt_params prm, double* out)

@@ -55,6 +55,8 @@ struct rt_ctx {
 	                                       //   2 one walk kernel with the candidates batched per warp and primitive kind (device/rt_shadow_wb.cuh)
 	bool kind_present[6] = {false, false, false, false, false, false}; // primitive kinds of the uploaded scene (a queue and a launch per kind present)
 	unsigned long long rounds = 0;
+	uint8_t* stage = nullptr;              // page-locked staging of rt_render_tiles' packed tiles
+	size_t stage_bytes = 0;
 	void* static_scratch = nullptr;        // device address of g_static_scratch on this context's GPU (rt_intersect_static)
 	// optional per-stage timing
 	bool profile = false;
@@ -69,7 +71,7 @@ namespace {
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
        B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
-       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_COUNT };
+       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -507,6 +509,7 @@ void rt_destroy(rt_ctx* ctx)
 		if (ctx->buf[i]) cudaFree(ctx->buf[i]);
 	for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
 	if (ctx->pinned) cudaFreeHost(ctx->pinned);
+	if (ctx->stage) cudaFreeHost(ctx->stage);
 	if (ctx->ev_round) cudaEventDestroy(ctx->ev_round);
 	for (int k = 0; k < 2; k++) { if (ctx->ev_shade[k]) cudaEventDestroy(ctx->ev_shade[k]); if (ctx->ev_shadow[k]) cudaEventDestroy(ctx->ev_shadow[k]); }
 	for (int k = 0; k < 2; k++)
@@ -837,17 +840,57 @@ rt_status rt_render_tiles(rt_ctx* ctx, const rt_params* p, int w, int h, int par
 		CK(cudaStreamSynchronize(ctx->stream));
 		return RT_OK;
 	}
-	// copy only this partition's tiles: leave the caller's other pixels untouched
-	std::vector<uint8_t> tmp((size_t)w * h * 3);
-	CK(cudaMemcpyAsync(tmp.data(), dev, tmp.size(), cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	// only this partition's tiles cross the bus: packed on the device, one copy into page-locked staging, scattered into
+	// the caller's frame (its other pixels are left untouched)
 	const int tiles_x = (w + RT_TILE - 1) / RT_TILE, tiles_y = (h + RT_TILE - 1) / RT_TILE;
-	for (int t = part; t < tiles_x * tiles_y; t += n_parts) {
-		const int x0 = (t % tiles_x) * RT_TILE, y0 = (t / tiles_x) * RT_TILE;
+	const long long n_tiles = (long long)tiles_x * tiles_y;
+	const long long n_local = (n_tiles - part + n_parts - 1) / n_parts;
+	const size_t bytes = (size_t)n_local * RT_TILE_PIX * 3;
+	if (n_local <= 0) return RT_OK;
+	if ((st = ensure(ctx, B_PACKED, bytes)) != RT_OK) return st;
+	if (ctx->stage_bytes < bytes) {
+		if (ctx->stage) cudaFreeHost(ctx->stage);
+		ctx->stage = nullptr;
+		ctx->stage_bytes = 0;
+		CK(cudaMallocHost((void**)&ctx->stage, bytes));
+		ctx->stage_bytes = bytes;
+	}
+	k_pack_tiles<<<blocks_for(n_local * RT_TILE_PIX, 256), 256, 0, ctx->stream>>>((const uint8_t*)dev, w, h, tiles_x, part, n_parts, n_local, (uint8_t*)ctx->buf[B_PACKED]);
+	CK(cudaGetLastError());
+	CK(cudaMemcpyAsync(ctx->stage, ctx->buf[B_PACKED], bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	for (long long lt = 0; lt < n_local; lt++) {
+		const long long t = lt * n_parts + part;
+		const int x0 = (int)(t % tiles_x) * RT_TILE, y0 = (int)(t / tiles_x) * RT_TILE;
 		const int x1 = x0 + RT_TILE < w ? x0 + RT_TILE : w, y1 = y0 + RT_TILE < h ? y0 + RT_TILE : h;
 		for (int j = y0; j < y1; j++)
-			std::memcpy(rgb_out + ((size_t)j * w + x0) * 3, tmp.data() + ((size_t)j * w + x0) * 3, (size_t)(x1 - x0) * 3);
+			std::memcpy(rgb_out + ((size_t)j * w + x0) * 3, ctx->stage + ((size_t)lt * RT_TILE_PIX + (size_t)(j - y0) * RT_TILE) * 3, (size_t)(x1 - x0) * 3);
 	}
+	return RT_OK;
+}
+
+rt_status rt_pack_tiles(rt_ctx* ctx, const void* dev_rgb, int w, int h, int part, int n_parts, void* dev_packed)
+{
+	if (!ctx) return RT_ERR_ARG;
+	if (!dev_rgb || !dev_packed || w <= 0 || h <= 0 || n_parts <= 0 || part < 0 || part >= n_parts) { ctx->error = "bad arguments"; return RT_ERR_ARG; }
+	CK(cudaSetDevice(ctx->device));
+	const int tiles_x = (w + RT_TILE - 1) / RT_TILE, tiles_y = (h + RT_TILE - 1) / RT_TILE;
+	const long long n_local = ((long long)tiles_x * tiles_y - part + n_parts - 1) / n_parts;
+	if (n_local > 0) k_pack_tiles<<<blocks_for(n_local * RT_TILE_PIX, 256), 256, 0, ctx->stream>>>((const uint8_t*)dev_rgb, w, h, tiles_x, part, n_parts, n_local, (uint8_t*)dev_packed);
+	CK(cudaGetLastError());
+	CK(cudaStreamSynchronize(ctx->stream));
+	return RT_OK;
+}
+
+rt_status rt_unpack_tiles(rt_ctx* ctx, const void* dev_gathered, int w, int h, int n_parts, long long tiles_cap, void* dev_rgb_out)
+{
+	if (!ctx) return RT_ERR_ARG;
+	const long long need = ((long long)((w + RT_TILE - 1) / RT_TILE) * ((h + RT_TILE - 1) / RT_TILE) + n_parts - 1) / (n_parts > 0 ? n_parts : 1);
+	if (!dev_gathered || !dev_rgb_out || w <= 0 || h <= 0 || n_parts <= 0 || tiles_cap < need) { ctx->error = "bad arguments"; return RT_ERR_ARG; }
+	CK(cudaSetDevice(ctx->device));
+	k_unpack_tiles<<<blocks_for((long long)w * h, 256), 256, 0, ctx->stream>>>((const uint8_t*)dev_gathered, w, h, (w + RT_TILE - 1) / RT_TILE, n_parts, tiles_cap, (uint8_t*)dev_rgb_out);
+	CK(cudaGetLastError());
+	CK(cudaStreamSynchronize(ctx->stream));
 	return RT_OK;
 }
 

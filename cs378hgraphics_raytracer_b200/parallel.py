@@ -71,6 +71,36 @@ def gather_frame(frame, rank, world, dst=0):
     return unpack_tiles([recv[r] for r in range(world)], w, h, world)
 
 
+_gather_bufs = {}
+
+
+def gather_frame_device(ctx, ptr, w, h, rank, world, device, dst=0):
+    """Framebuffer gather of the device frame rt_render_device left at `ptr`: the rank's tiles are packed by a device kernel
+    (rt_pack_tiles), ONE gather sends each rank's block to rank `dst` only (NCCL send / recv; 1 / world of the frame per
+    rank instead of the whole frame to everyone), rank dst un-interleaves with a device kernel (rt_unpack_tiles).
+    torch only carries the bytes.  Returns the (h, w, 3) device frame on dst, None elsewhere; buffers are reused."""
+    tx, ty = tile_grid(w, h)
+    cap = (tx * ty + world - 1) // world
+    key = (w, h, world, str(device))
+    if key not in _gather_bufs:
+        packed = torch.zeros((cap, TILE * TILE * 3), dtype=torch.uint8, device=device)
+        big = torch.empty((world, cap, TILE * TILE * 3), dtype=torch.uint8, device=device) if rank == dst else None
+        full = torch.empty((h, w, 3), dtype=torch.uint8, device=device) if rank == dst else None
+        _gather_bufs[key] = (packed, big, full)
+    packed, big, full = _gather_bufs[key]
+    ctx.pack_tiles(int(ptr), w, h, rank, world, packed.data_ptr())
+    if world > 1:
+        torch.cuda.current_stream(device).synchronize()  # the library's stream finished the pack (the call is synchronous); order torch's stream after it
+        dist.gather(packed, list(big.unbind(0)) if rank == dst else None, dst=dst)
+    elif rank == dst:
+        big[0].copy_(packed)
+    if rank != dst:
+        return None
+    torch.cuda.current_stream(device).synchronize()
+    ctx.unpack_tiles(big.data_ptr(), w, h, world, cap, full.data_ptr())
+    return full
+
+
 def broadcast_arena(arena_bytes, rank, world, device, src=0):
     """Scene broadcast: rank `src` holds the flattened arena (host bytes); everyone gets a copy."""
     if world == 1:

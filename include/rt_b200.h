@@ -124,6 +124,14 @@ rt_status rt_render_tiles(rt_ctx* ctx, const rt_params* p, int w, int h, int par
 rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int part, int n_parts,
                            void** dev_rgb, rt_stats* stats);
 
+/* Framebuffer gather of the tile partition (the reference's pixel loop has no counterpart - its OpenMP
+ * threads share one buffer, RayTracer.cpp:283-313).  rt_pack_tiles: a rank's tiles of the device frame `dev_rgb` as one
+ * contiguous device block `dev_packed` of ceil((tiles - part) / n_parts) * 3072 bytes (32 x 32 x RGB per tile, tile order)
+ * - what is sent to the gathering rank.  rt_unpack_tiles: the inverse on the gathering rank; dev_gathered holds n_parts
+ * blocks of tiles_cap packed tiles (rank r's tiles in block r), dev_rgb_out receives the w*h*3 frame. */
+rt_status rt_pack_tiles(rt_ctx* ctx, const void* dev_rgb, int w, int h, int part, int n_parts, void* dev_packed);
+rt_status rt_unpack_tiles(rt_ctx* ctx, const void* dev_gathered, int w, int h, int n_parts, long long tiles_cap, void* dev_rgb_out);
+
 /* RayTracer::tracePixel(i,j) for n pixels (RayTracer.cpp:81-102): rgb_out[3n] doubles, clamped
  * like the reference, not quantised.  ij = {i0,j0,i1,j1,...}. */
 rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const int32_t* ij, int n,

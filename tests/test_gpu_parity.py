@@ -510,3 +510,30 @@ def test_full_size_frame_windows(rtlib, oracle_mod, tmp_path_factory, key):
         assert cam == st_full.camera_rays
     finally:
         c.close()
+
+
+@pytest.mark.parametrize("w,h", [(200, 150), (64, 32), (33, 1)])
+def test_pack_unpack_tiles_device(rtlib, ctx, scene_dir, w, h):
+    """rt_pack_tiles / rt_unpack_tiles (the multi-GPU frame gather's two device kernels): every partition of an n-way
+    split rendered, packed into its block of the gather buffer and un-interleaved gives the single-partition frame;
+    the packed block equals the torch restatement of the tile math (parallel.pack_tiles, the one the gloo tests use)."""
+    import torch
+    from cs378hgraphics_raytracer_b200 import parallel as par
+    arena = rtlib.load_ray_file(str(scene_dir / "hitchcock.ray"))
+    ctx.upload(arena)
+    p = rtlib.Params.default(depth=3)
+    full, _ = ctx.render(p, w, h)
+    dev = torch.device("cuda", 0)
+    tx, ty = par.tile_grid(w, h)
+    for n in (1, 2, 3, 8):
+        cap = (tx * ty + n - 1) // n
+        big = torch.zeros((n, cap, 32 * 32 * 3), dtype=torch.uint8, device=dev)
+        for part in range(n):
+            ptr, _ = ctx.render_device(p, w, h, part, n)
+            ctx.pack_tiles(int(ptr), w, h, part, n, big[part].data_ptr())
+            want = par.pack_tiles(par.device_frame(ptr, w, h, dev), part, n)
+            assert torch.equal(big[part][:want.shape[0]], want)
+        out = torch.zeros((h, w, 3), dtype=torch.uint8, device=dev)
+        ctx.unpack_tiles(big.data_ptr(), w, h, n, cap, out.data_ptr())
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy(), full)

@@ -5,5 +5,5 @@ tests and bench.py.  There is no Python or CPU implementation of the trace loop 
 library is missing or no CUDA device is usable, the calls raise.
 """
 from .binding import (  # noqa: F401
-    LIB_PATH, RtError, Params, Stats, Ray, Hit, HIT_DTYPE, lib, load_ray_file, Arena, Context, build_library, write_image, read_image, save_arena, load_arena,
+    LIB_PATH, RtError, Params, Stats, Ray, Hit, HIT_DTYPE, lib, load_ray_file, Arena, Context, build_library, write_image, read_image, save_arena, load_arena, MultiContext,
 )

@@ -93,6 +93,21 @@ def lib():
                                    ctypes.POINTER(vp), ctypes.POINTER(Stats)]
     L.rt_trace_pixels.argtypes = [vp, ctypes.POINTER(Params), ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, vp]
     L.rt_trace_rays.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, ctypes.c_int, vp, vp]
+    L.rt_multi_create.argtypes = [ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.POINTER(vp)]
+    L.rt_multi_create.restype = i32
+    L.rt_multi_destroy.argtypes = [vp]
+    L.rt_multi_destroy.restype = None
+    L.rt_multi_last_error.argtypes = [vp]
+    L.rt_multi_last_error.restype = cp
+    L.rt_multi_devices.argtypes = [vp]
+    L.rt_multi_upload_scene.argtypes = [vp, vp, sz]
+    L.rt_multi_upload_scene.restype = i32
+    L.rt_multi_render.argtypes = [vp, ctypes.POINTER(Params), ctypes.c_int, ctypes.c_int, vp, ctypes.POINTER(Stats)]
+    L.rt_multi_render.restype = i32
+    L.rt_scene_buffer.argtypes = [vp, sz, ctypes.POINTER(vp)]
+    L.rt_scene_buffer.restype = i32
+    L.rt_upload_scene_resident.argtypes = [vp, vp, sz]
+    L.rt_upload_scene_resident.restype = i32
     L.rt_pack_tiles.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp]
     L.rt_pack_tiles.restype = i32
     L.rt_unpack_tiles.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_longlong, vp]
@@ -310,3 +325,34 @@ class Context:
         self._check(lib().rt_trace_rays(self._h, ctypes.byref(params), rays.ctypes.data, n, depth,
                                         hits.ctypes.data if want_hits else None, rgb.ctypes.data if want_rgb else None))
         return hits, rgb
+
+
+class MultiContext:
+    """rt_multi_*: N GPUs of one box in ONE process (scene replicated by NCCL broadcast, interleaved tiles, gather to
+    the first device).  No fallback: fails loudly without the devices, or - for N > 1 - without NCCL."""
+
+    def __init__(self, devices):
+        arr = (ctypes.c_int * len(devices))(*devices)
+        h = ctypes.c_void_p()
+        st = lib().rt_multi_create(arr, len(devices), ctypes.byref(h))
+        if st != 0:
+            raise RtError(st, "rt_multi_create(%s) failed" % list(devices))
+        self._h = h
+
+    def _check(self, st):
+        if st != 0:
+            raise RtError(st, lib().rt_multi_last_error(self._h).decode(errors="replace"))
+
+    def upload(self, arena):
+        self._check(lib().rt_multi_upload_scene(self._h, arena.ptr, arena.nbytes))
+
+    def render(self, params, w, h):
+        out = np.zeros((h, w, 3), np.uint8)
+        st = Stats()
+        self._check(lib().rt_multi_render(self._h, ctypes.byref(params), w, h, out.ctypes.data, ctypes.byref(st)))
+        return out, st
+
+    def close(self):
+        if self._h:
+            lib().rt_multi_destroy(self._h)
+            self._h = None

@@ -6,7 +6,7 @@
 
 namespace rtb200 {
 
-RayTracer::RayTracer(int device) : stopTrace(false), ctx(nullptr), arena(nullptr), arena_bytes(0), loaded(false), buffer_width(256), buffer_height(256)
+RayTracer::RayTracer(int device) : stopTrace(false), ctx(nullptr), multi(nullptr), arena(nullptr), arena_bytes(0), loaded(false), buffer_width(256), buffer_height(256)
 {
 	rt_params_default(&ui);
 	std::memset(&stats, 0, sizeof(stats));
@@ -19,7 +19,24 @@ RayTracer::RayTracer(int device) : stopTrace(false), ctx(nullptr), arena(nullptr
 RayTracer::~RayTracer()
 {
 	if (arena) rt_arena_free(arena);
-	if (ctx) rt_destroy(ctx);
+	if (multi) rt_multi_destroy(multi); // owns ctx
+	else if (ctx) rt_destroy(ctx);
+}
+
+bool RayTracer::useDevices(int n)
+{
+	if (n <= 1) return ctx != nullptr;
+	std::vector<int> dev(n);
+	for (int k = 0; k < n; k++) dev[k] = k;
+	rt_multi* m = nullptr;
+	const rt_status st = rt_multi_create(dev.data(), n, &m);
+	if (st != RT_OK) { alert(st == RT_ERR_NO_DEVICE ? "not that many CUDA devices" : (st == RT_ERR_UNSUPPORTED ? "NCCL is not available" : "rt_multi_create failed")); return false; }
+	if (ctx && !multi) rt_destroy(ctx);
+	if (multi) rt_multi_destroy(multi);
+	multi = m;
+	ctx = rt_multi_context(m, 0);
+	loaded = false;
+	return true;
 }
 
 void RayTracer::alert(const std::string& msg)
@@ -37,8 +54,8 @@ bool RayTracer::loadScene(const char* fn)
 	for (int k = 0; k < 6 && cubemap.size() == 6; k++) faces[k] = cubemap[k].c_str();
 	rt_status st = rt_load_ray_file(fn, cubemap.size() == 6 ? faces : nullptr, &arena, &arena_bytes);
 	if (st != RT_OK) { alert(rt_host_last_error()); return false; } // the reference alerts the parser's message and returns false
-	st = rt_upload_scene(ctx, arena, arena_bytes);
-	if (st != RT_OK) { alert(rt_last_error(ctx)); return false; }
+	st = multi ? rt_multi_upload_scene(multi, arena, arena_bytes) : rt_upload_scene(ctx, arena, arena_bytes);
+	if (st != RT_OK) { alert(multi ? rt_multi_last_error(multi) : rt_last_error(ctx)); return false; }
 	loaded = true;
 	return true;
 }
@@ -65,8 +82,8 @@ void RayTracer::traceImage(int w, int h)
 {
 	traceSetup(w, h);
 	if (!loaded) return;
-	const rt_status st = rt_render(ctx, &ui, w, h, buffer.data(), &stats);
-	if (st != RT_OK) alert(rt_last_error(ctx));
+	const rt_status st = multi ? rt_multi_render(multi, &ui, w, h, buffer.data(), &stats) : rt_render(ctx, &ui, w, h, buffer.data(), &stats);
+	if (st != RT_OK) alert(multi ? rt_multi_last_error(multi) : rt_last_error(ctx));
 }
 
 dvec3 RayTracer::tracePixel(int i, int j)

@@ -21,6 +21,9 @@ struct ray {
 class RayTracer {
 public:
 	explicit RayTracer(int device = 0);
+	// Renders on devices 0 .. n-1 of the box (rt_multi_*: scene replicated, interleaved tiles); call before loadScene.
+	// The reference's counterpart is its thread count (-t, main.cpp:12): parallelism inside traceImage.
+	bool useDevices(int n);
 	~RayTracer();
 	RayTracer(const RayTracer&) = delete;
 	RayTracer& operator=(const RayTracer&) = delete;
@@ -53,6 +56,7 @@ public:
 private:
 	void alert(const std::string& msg);
 	rt_ctx* ctx;
+	rt_multi* multi; // non-null after useDevices(n > 1): ctx is then its first device's context
 	void* arena;
 	size_t arena_bytes;
 	bool loaded;

@@ -1,6 +1,6 @@
 // main_cli.cpp - `ray_b200`: the reference's command line (ui/CommandLineUI.cpp:25-147) in front of
 // the device path.  Same options and option grammar (-O <mode> followed by -A/-B/-C values):
-//   ray_b200 [-r depth] [-w width] [-c cubemap_file] [-O a|j|r|o|d|g|c|s] [-A v] [-B v] [-C v] in.ray out.png|out.bmp
+//   ray_b200 [-r depth] [-w width] [-c cubemap_file] [-O a|j|r|o|d|g|c|s] [-A v] [-B v] [-C v] [-g gpus] in.ray out.png|out.bmp
 // The output format follows the extension as the reference's writeImage does (PNG through zlib, else BMP); -j (json settings) and -t are not mirrored.
 #include <dirent.h>
 #include <unistd.h>
@@ -20,6 +20,7 @@ static void usage(const char* prog)
 	                     "  -c <file>   one of the six cubemap images (the others are found next to it)\n"
 	                     "  -O a|j|r    adaptive / jittered / supersampled AA; -A samples, -B threshold (adaptive)\n"
 	                     "  -O d        depth of field; -A focal distance, -B subdivisions, -C aperture\n"
+	                     "  -g <#>      render on that many GPUs of this box (interleaved tiles, scene replicated)\n"
 	                     "  -O g        anaglyph   -O o  overlapping objects   -O c -A thr  adaptive termination\n", prog);
 }
 
@@ -49,11 +50,12 @@ int main(int argc, char** argv)
 	std::string cubemap_file;
 	char prev = 0;
 	int c;
-	while ((c = getopt(argc, argv, "r:w:hc:O:A:B:C:")) != EOF) {
+	while ((c = getopt(argc, argv, "r:w:hc:O:A:B:C:g:")) != EOF) {
 		switch (c) {
 		case 'r': tracer.ui.depth = std::atoi(optarg); break;
 		case 'w': size = std::atoi(optarg); break;
 		case 'c': cubemap_file = optarg; break;
+		case 'g': if (!tracer.useDevices(std::atoi(optarg))) return 1; break;
 		case 'O':
 			prev = *optarg;
 			switch (prev) {

@@ -572,7 +572,24 @@ static rt_status derive_trees(rt_ctx* ctx, const rt_node* nodes, long long cnt, 
 	return RT_OK;
 }
 
-rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
+static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes, bool resident);
+rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes) { return upload_scene_impl(ctx, arena, bytes, false); }
+// The two halves of rt_upload_scene for a scene that reaches the device by another road (the NCCL broadcast of
+// rt_multi_upload_scene): rt_scene_buffer hands out the context's arena buffer, rt_upload_scene_resident does everything
+// rt_upload_scene does except the host -> device copy (`arena` = the same bytes in host memory, for the small tables).
+rt_status rt_scene_buffer(rt_ctx* ctx, size_t bytes, void** dev)
+{
+	if (!ctx || !dev || bytes == 0) return RT_ERR_ARG;
+	CK(cudaSetDevice(ctx->device));
+	ctx->has_scene = false;
+	const rt_status st = ensure(ctx, B_ARENA, bytes);
+	if (st != RT_OK) return st;
+	*dev = ctx->buf[B_ARENA];
+	return RT_OK;
+}
+rt_status rt_upload_scene_resident(rt_ctx* ctx, const void* arena, size_t bytes) { return upload_scene_impl(ctx, arena, bytes, true); }
+
+static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes, bool resident)
 {
 	if (!ctx) return RT_ERR_ARG;
 	// header, section table and the small tables are checked here; the O(scene) index checks run
@@ -606,7 +623,7 @@ rt_status rt_upload_scene(rt_ctx* ctx, const void* arena, size_t bytes)
 	// one copy of the whole arena
 	if ((st = ensure(ctx, B_ARENA, bytes)) != RT_OK) return st;
 	uint8_t* dev = (uint8_t*)ctx->buf[B_ARENA];
-	CK(cudaMemcpyAsync(dev, arena, bytes, cudaMemcpyHostToDevice, ctx->stream));
+	if (!resident) CK(cudaMemcpyAsync(dev, arena, bytes, cudaMemcpyHostToDevice, ctx->stream));
 	DScene& S = ctx->S;
 	std::memset(&S, 0, sizeof(S));
 #define SEC(field, type, sec) S.field = (const type*)(dev + A.hdr->sections[sec].offset)

@@ -132,6 +132,28 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 rt_status rt_pack_tiles(rt_ctx* ctx, const void* dev_rgb, int w, int h, int part, int n_parts, void* dev_packed);
 rt_status rt_unpack_tiles(rt_ctx* ctx, const void* dev_gathered, int w, int h, int n_parts, long long tiles_cap, void* dev_rgb_out);
 
+/* The two halves of rt_upload_scene for a scene whose bytes reach the device by another road (rt_multi_upload_scene's NCCL
+ * broadcast): rt_scene_buffer hands out the context's scene buffer (device pointer, >= bytes), rt_upload_scene_resident does
+ * all of rt_upload_scene except the host -> device copy; `arena` = the same bytes in host memory (small tables are read there). */
+rt_status rt_scene_buffer(rt_ctx* ctx, size_t bytes, void** dev);
+rt_status rt_upload_scene_resident(rt_ctx* ctx, const void* arena, size_t bytes);
+
+/* ---- N GPUs of one box in one process -----------------------------------------------------------
+ * Replaces the reference's parallel driver INSIDE RayTracer::traceImage (the OpenMP pixel loop, RayTracer.cpp:283-285):
+ * one context per device, one host thread per device during a call, scene replicated (one host -> device copy + ncclBroadcast),
+ * image split into interleaved 32x32 tiles (tile t -> device t mod N), packed tiles sent to the first device with grouped
+ * ncclSend / ncclRecv and un-interleaved there.  NCCL is loaded at run time (dlopen): n_dev == 1 needs no NCCL at all.
+ * rt_multi_render's stats are summed over the devices (device_ms: the slowest). */
+typedef struct rt_multi rt_multi;
+rt_status rt_multi_create(const int* devices, int n_dev, rt_multi** out);
+void rt_multi_destroy(rt_multi* m);
+const char* rt_multi_last_error(const rt_multi* m);
+int rt_multi_devices(const rt_multi* m);
+/* the r-th device's context (owned by m): rt_trace_pixels / rt_trace_rays of the replicated scene run on any one of them */
+rt_ctx* rt_multi_context(rt_multi* m, int r);
+rt_status rt_multi_upload_scene(rt_multi* m, const void* arena, size_t bytes);
+rt_status rt_multi_render(rt_multi* m, const rt_params* p, int w, int h, uint8_t* rgb_out, rt_stats* stats);
+
 /* RayTracer::tracePixel(i,j) for n pixels (RayTracer.cpp:81-102): rgb_out[3n] doubles, clamped
  * like the reference, not quantised.  ij = {i0,j0,i1,j1,...}. */
 rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const int32_t* ij, int n,

@@ -537,3 +537,31 @@ def test_pack_unpack_tiles_device(rtlib, ctx, scene_dir, w, h):
         ctx.unpack_tiles(big.data_ptr(), w, h, n, cap, out.data_ptr())
         torch.cuda.synchronize()
         assert np.array_equal(out.cpu().numpy(), full)
+
+
+def test_multi_gpu_abi(rtlib, ctx, scene_dir):
+    """rt_multi_* (N GPUs in one process behind the C ABI: NCCL broadcast of the arena, interleaved tiles, packed tiles sent
+    to the first device): the frame and the summed ray counts equal the single-context ones.  One device always; two (and
+    every device of the box) where the box has them - the round's 1-GPU run covers the degenerate case only."""
+    import torch
+    arena = rtlib.load_ray_file(str(scene_dir / "prims_mixed.ray"))
+    ctx.upload(arena)
+    p = rtlib.Params.default(depth=5)
+    w, h = 200, 150
+    full, st_full = ctx.render(p, w, h)
+    n_dev = torch.cuda.device_count()
+    for devices in [[0]] + ([[0, 1]] if n_dev >= 2 else []) + ([list(range(n_dev))] if n_dev > 2 else []):
+        m = rtlib.MultiContext(devices)
+        try:
+            m.upload(arena)
+            for _ in range(2):  # buffers are reused on the second call
+                img, st = m.render(p, w, h)
+                _assert_same_frame(img, full)
+                assert (st.camera_rays, st.reflection_rays, st.refraction_rays, st.shadow_rays) == \
+                    (st_full.camera_rays, st_full.reflection_rays, st_full.refraction_rays, st_full.shadow_rays)
+        finally:
+            m.close()
+    with pytest.raises(rtlib.RtError):
+        rtlib.MultiContext([0, 0])  # one rank per GPU
+    with pytest.raises(rtlib.RtError):
+        rtlib.MultiContext([n_dev])

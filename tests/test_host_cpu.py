@@ -350,3 +350,28 @@ def test_adapt_aa_known_answer(oracle_mod):
     area, check = float(m.group(1)), float(m.group(2))
     assert out.strip() == "area = 0.786317 (check= 0.785398)"
     assert abs(check - np.pi / 4) < 1e-6 and abs(area - check) < 2e-3
+
+
+def test_overlapping_objects_mode_has_no_reference_result(oracle_mod, ref_scene_dir):
+    """Why rt_render answers RT_ERR_UNSUPPORTED for -O o (Scene::discoverMat, scene.cpp:212-237): isect::checkObj
+    (scene/ray.cpp:43-45) has no return statement.  g++ -O2 compiles it without a `ret` (the virtual call to
+    Geometry::check is followed by padding and the next function, MaterialSceneObject::getMaterial, whose `ret` then pops a
+    misaligned slot), so the UNMODIFIED reference dies with SIGSEGV as soon as discoverMat meets an entering surface behind a
+    leaving one - which its own fixture for this mode, newScene/spheres_overlap.ray, does at any depth that recurses.
+    Where checkObj is never reached the run completes (depth 0: shadow rays only)."""
+    import sys
+    prog = ("import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+            "import cs378hgraphics_raytracer_b200 as rt, oracle_binding as ob\n"
+            "o = ob.Oracle(sys.argv[1]); ob.ref().ref_set_threads(1)\n"
+            "img, st, _ = o.render(rt.Params.default(depth=int(sys.argv[2]), overlapping_objects=1), 64, 64)\n"
+            "print('completed', int(img.sum()))\n") % (ROOT, os.path.join(ROOT, "tests"))
+    scene = str(ref_scene_dir / "spheres_overlap.ray")
+    ok = subprocess.run([sys.executable, "-c", prog, scene, "0"], capture_output=True, text=True, timeout=300)
+    assert ok.returncode == 0 and "completed" in ok.stdout, ok.stderr[-500:]
+    bad = subprocess.run([sys.executable, "-c", prog, scene, "5"], capture_output=True, text=True, timeout=300)
+    assert bad.returncode != 0 and "completed" not in bad.stdout  # SIGSEGV (-11) in the builds seen so far
+    # the compiled function really has no way back: no `ret` between its entry and the next symbol
+    dis = subprocess.run(["objdump", "-d", "--no-show-raw-insn", "-C", os.path.join(ROOT, "oracle", "_ref", "libref_oracle.so")],
+                         capture_output=True, text=True).stdout
+    body = dis.split("<isect::checkObj(isect const&, isect const&)>:")[1].split("\n\n")[0]
+    assert "call" in body and "ret" not in body, body

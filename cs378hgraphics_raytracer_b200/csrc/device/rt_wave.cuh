@@ -26,6 +26,13 @@
 
 namespace rtd {
 
+// A ray that exhausts its node budget does not hold up its round: k_wave_closest marks its hit record RT_T_DEFERRED, k_wave_shade
+// copies the ray unchanged into the next round's queue with this bit set, and there it is walked with 16 x the budget at the
+// front of the launch, beside that round's ordinary rays.  A frame then pays the tail of its longest closest-hit walks once,
+// in its last round, instead of once per recursion level (what limits tile-parallel scaling: the tails do not shrink with
+// the partition).  The winner of a walk does not depend on when it is walked, and a deferred ray is counted when it is shaded.
+#define META_DEFERRED (1 << 16)
+#define RT_T_DEFERRED (-2.0)
 enum { KIND_DEAD = 7 }; // a primary slot outside the image (edge tiles): skipped by every stage
 
 #define RT_WAVE_THREADS 128
@@ -71,6 +78,7 @@ struct WaveCounters {
 	unsigned long long heavy_cursor; // next heavy ray to be taken by a warp
 	unsigned long long n_retry;      // rays that exhausted the FIRST budget (k_wave_closest); k_wave_closest_retry walks them
 	                                 // again with a larger one and only its leftovers (n_heavy) go to the cooperative kernel
+	unsigned long long n_deferred;   // rays that exhausted the first budget and were put off to the next round (META_DEFERRED)
 	unsigned long long n_shadow[2];  // per round parity: the shadow rays of round r are still being
 	                                 // walked (second stream) while round r+1 fills the other queue
 };
@@ -130,9 +138,15 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 // and refraction rays arrive in the order their parents were shaded; sorted by direction octant and origin cell, the rays
 // of a warp walk the same subtrees).  Hit records stay indexed by queue slot, so the shade stage does not care.
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
-                                                                                    int budget, int* retry, unsigned long long* n_retry, const unsigned* __restrict__ perm, long long n_perm)
+                                                                                    int budget, int* retry, unsigned long long* n_retry, const unsigned* __restrict__ perm, long long n_perm,
+                                                                                    unsigned long long* n_deferred, int sparse)
 {
-	const long long k0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
+	// sparse > 0 (a round too small to fill the GPU): one ray per 2^sparse lanes.  A warp's time is the SUM of the divergent
+	// paths of its rays, a few lanes at a time; with fewer rays per warp and more warps the launch ends sooner, and the lanes
+	// left idle would have had nothing to do anyway.
+	const long long t0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
+	if (t0 & ((1ll << sparse) - 1)) return;
+	const long long k0 = t0 >> sparse;
 	if (k0 >= m) return;
 	const long long k = k0 < n_perm ? (long long)perm[k0] : k0;
 	const long long q = base + k;
@@ -148,7 +162,13 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_clos
 	SBuf unused;
 	unused.n = 0;
 	unused.cut = RT_T_INF;
-	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, budget)) {
+	const bool second_try = (meta & META_DEFERRED) != 0;
+	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, second_try ? budget * 16 : budget)) {
+		if (n_deferred && !second_try) { // put off to the next round (n_deferred == NULL: deferral is off)
+			H.t[k] = RT_T_DEFERRED;
+			atomicAdd(n_deferred, 1ull);
+			return;
+		}
 		retry[atomicAdd(n_retry, 1ull)] = (int)k; // k_wave_closest_retry (or, with a forced budget, the cooperative kernel) redoes this ray
 		return;
 	}
@@ -249,6 +269,9 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 	MatEval me;
 	Hit h;
 	d3 w = mk3(0, 0, 0), hitP = mk3(0, 0, 0), rd = mk3(0, 0, 1);
+	// a ray whose walk was put off: it travels to the next round as it is, uncounted and unshaded
+	const bool deferred = live && H.t[k] == RT_T_DEFERRED;
+	if (deferred) live = false;
 	if (live) {
 		const int kind = (meta >> 12) & 15;
 		const d3 ro = Q.load_v(0, q);
@@ -284,6 +307,19 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 			Nxt.store_v(6, s, kid[c].weight);
 			Nxt.store_v(9, s, kid[c].att_kt);
 			Nxt.store_meta(s, sample, pack_meta(kid[c].depth, kid[c].att_mode, kid[c].kind, 0));
+		}
+	}
+	{
+		const long long s = wave_reserve(deferred, lt_mask, &cnt->n_children);
+		if (s >= 0) {
+			if (s >= Nxt.cap) overflow = 1;
+			else {
+				Nxt.store_v(0, s, Q.load_v(0, q));
+				Nxt.store_v(3, s, Q.load_v(3, q));
+				Nxt.store_v(6, s, Q.load_v(6, q));
+				Nxt.store_v(9, s, Q.load_v(9, q));
+				Nxt.store_meta(s, sample, meta | META_DEFERRED);
+			}
 		}
 	}
 	// one shadow ray per light (Material::shade's loop, material.cpp:50-66), light by light so
@@ -418,9 +454,11 @@ __global__ void __launch_bounds__(256) k_closest_keys(const __grid_constant__ DS
 
 // perm: NULL, or the order in which the queue's rays are taken (k_shadow_keys + radix sort); n = rays in the queue
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt,
-                                                                                const unsigned* __restrict__ perm)
+                                                                                const unsigned* __restrict__ perm, int sparse)
 {
-	const long long k0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
+	const long long t0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
+	if (t0 & ((1ll << sparse) - 1)) return; // one ray per 2^sparse lanes in rounds too small to fill the GPU (see k_wave_closest)
+	const long long k0 = t0 >> sparse;
 	long long n = (long long)cnt->n_shadow[parity];
 	if (n > SQ.cap) n = SQ.cap;
 	if (k0 >= n) return;

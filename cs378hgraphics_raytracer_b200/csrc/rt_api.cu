@@ -47,6 +47,8 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
+	bool sparse_small = true;              // RT_B200_SPARSE=0: small rounds are launched densely (32 rays per warp) like large ones
+	bool defer_long = false;               // RT_B200_DEFER=0: rays that exhaust the node budget are retried in their own round instead of the next one
 	bool sort_closest = true;              // RT_B200_SORTC=0: reflection / refraction rays are walked in queue order instead of (octant, origin cell) order
 	bool sort_shadow = true;               // RT_B200_SORT=0: shadow rays are walked in queue order instead of (light, origin cell) order
 	int shadow_mode = 0;                   // how a round's shadow rays are walked (RT_B200_SHADOW=one|split|wb):
@@ -125,6 +127,15 @@ rt_status check_params(rt_ctx* ctx, const rt_params* p)
 }
 
 #define RT_SORT_MIN (1ll << 20) // rounds with fewer possible shadow rays are walked in queue order (a sort is ~20 us of launches)
+// log2 of the lanes given to one ray of a walk launch over n rays: as many as keep the launch within the GPU's resident threads
+static inline int sparse_shift(const rt_ctx* ctx, long long n)
+{
+	if (!ctx->sparse_small || n <= 0) return 0;
+	const long long resident = (long long)ctx->sm_count * 1024;
+	int s = 0;
+	while (s < 5 && (n << (s + 1)) <= resident) s++;
+	return s;
+}
 static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 rt_status make_queue(rt_ctx* ctx, int bd, int bi, long long cap, int nd, RayQueue& Q)
@@ -297,7 +308,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		}
 		if (m == 0) break;
 		const int par = (int)(round & 1);
-		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream));
+		CK(cudaMemsetAsync(&cnt->n_children, 0, 5 * sizeof(unsigned long long), ctx->stream)); // children, heavy, cursor, retry, deferred
 		// a forced budget (RT_B200_BUDGET, the tests) sends its leftovers straight to the cooperative kernel
 		const bool second = ctx->budget_auto && ctx->walk_budget > 0;
 		const unsigned* cperm = nullptr;
@@ -313,8 +324,10 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 			STAGE(RT_STAGE_OTHER, CK(cub::DeviceRadixSort::SortPairs(ctx->buf[B_CUBTMP3], tmp_bytes, keys, keys + W, idx, idx + W, (int)n_kids, 0, 30, ctx->stream)));
 			cperm = idx + W;
 		} else n_kids = 0;
-		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget,
-		                                                                                                                second ? retry : heavy, second ? &cnt->n_retry : &cnt->n_heavy, cperm, n_kids));
+		const int csh = sparse_shift(ctx, m);
+		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m << csh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget,
+		                                                                                                                second ? retry : heavy, second ? &cnt->n_retry : &cnt->n_heavy, cperm, n_kids,
+		                                                                                                                (second && ctx->defer_long) ? &cnt->n_deferred : nullptr, csh));
 		if (second) {
 			// second chance with 8 x the budget: grid for 1/32 of the round (a grid-stride loop takes whatever there is)
 			const unsigned rblocks = blocks_for((m + 31) / 32, RT_TRACE_THREADS);
@@ -328,7 +341,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		shadow_pending[par] = false;
 		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
-		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry, shadow rays [2]
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry, deferred, shadow rays [2]
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		// Large rounds: the shadow rays are walked in (light, origin cell) order.  The radix sort needs the number of rays on
 		// the host, which arrives with the counters the host waits for anyway - so the wait moves in front of the launch.
@@ -337,7 +350,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		if (sorted) {
 			CK(cudaEventSynchronize(ctx->ev_round));
 			synced = true;
-			long long ns = (long long)ctx->pinned[4 + par];
+			long long ns = (long long)ctx->pinned[5 + par];
 			if (ns > sq[par].cap) ns = sq[par].cap;
 			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
 			if (overlap) {
@@ -357,7 +370,8 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 				if ((st = ensure(ctx, bt, tmp_bytes)) != RT_OK) return st;
 				STAGE_ON(sstream, RT_STAGE_OTHER, k_shadow_keys<<<blocks_for(ns, 256), 256, 0, sstream>>>(ctx->S, sq[par], ns, keys, idx));
 				STAGE_ON(sstream, RT_STAGE_OTHER, CK(cub::DeviceRadixSort::SortPairs(ctx->buf[bt], tmp_bytes, keys, keys + sq[par].cap, idx, idx + sq[par].cap, (int)ns, 0, 32, sstream)));
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap));
+				const int ssh = sparse_shift(ctx, ns);
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, ssh));
 			}
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		} else if (L > 0) {
@@ -376,7 +390,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 				// the rays that met a transmissive / far-half surface (a few percent): the complete walk, persistent grid over the list
 				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow_list<<<(unsigned)ctx->sm_count * RT_SHADOW_MINB, RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], CQ));
 			} else
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr));
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for((m * L) << sparse_shift(ctx, m * L), RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr, sparse_shift(ctx, m * L)));
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
@@ -388,7 +402,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		// path gives the same hit, so this only moves work between the two kernels.
 		// (pinned[3]: the rays that ran out of the first budget.  A round walked before the budget has grown is not
 		// lost: its leftovers get a second single-thread chance, k_wave_closest_retry.)
-		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)ctx->pinned[3] * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
+		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)(ctx->pinned[3] + ctx->pinned[4]) * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
 		round++;
 		const RayQueue tmp = cur;
 		cur = nxt;
@@ -486,6 +500,8 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_DEFER")) ctx->defer_long = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_SPARSE")) ctx->sparse_small = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SHADOW")) ctx->shadow_mode = !strcmp(e, "one") ? 0 : (!strcmp(e, "split") ? 1 : 2);
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs

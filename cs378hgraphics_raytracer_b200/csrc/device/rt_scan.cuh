@@ -264,6 +264,31 @@ __device__ __forceinline__ unsigned cand_classify(const DScene& S, const d3& o, 
 	return fl;
 }
 
+// The shadow cache's test of ONE known candidate (k_wave_shadow phase 2): true when it alone settles srsAttenuation at 0.
+__device__ __noinline__ unsigned cand_test(const DScene& S, const d3& o, const d3& d, const rt_light& Lt, unsigned obj, unsigned pos)
+{
+	ShadowSide sd;
+	sd.limit = RT_T_INF;
+	sd.sure_t = RT_T_INF;
+	if (Lt.type == RT_LIGHT_POINT) { // shadow_begin's numbers (rt_traverse.cuh)
+		const double D = length(ld3(Lt.position) - o);
+		sd.limit = D * (1.0 + 1e-9) + 1e-9;
+		sd.sure_t = 0.49 * D;
+	} else if (Lt.type != RT_LIGHT_DIRECTIONAL) return 0u; // area and spot lights take no any-hit exit
+	sd.y[0] = 1.0 / d.x; sd.y[1] = 1.0 / d.y; sd.y[2] = 1.0 / d.z;
+	unsigned fl = 0;
+	switch (S.objs[obj].type) {
+	case RT_OBJ_SPHERE: fl = cand_classify<RT_OBJ_SPHERE>(S, o, d, sd, obj, pos); break;
+	case RT_OBJ_BOX: fl = cand_classify<RT_OBJ_BOX>(S, o, d, sd, obj, pos); break;
+	case RT_OBJ_SQUARE: fl = cand_classify<RT_OBJ_SQUARE>(S, o, d, sd, obj, pos); break;
+	case RT_OBJ_CYLINDER: fl = cand_classify<RT_OBJ_CYLINDER>(S, o, d, sd, obj, pos); break;
+	case RT_OBJ_CONE: fl = cand_classify<RT_OBJ_CONE>(S, o, d, sd, obj, pos); break;
+	case RT_OBJ_TRIMESH: fl = cand_classify<RT_OBJ_TRIMESH>(S, o, d, sd, obj, pos); break;
+	default: break;
+	}
+	return fl & SH_DEAD;
+}
+
 #define RT_CAND_THREADS 128
 template <int KIND>
 __global__ void __launch_bounds__(RT_CAND_THREADS) k_shadow_cand(const __grid_constant__ DScene S, const RayQueue SQ, const ShadowSide* __restrict__ side, unsigned* flags,

@@ -452,19 +452,36 @@ __global__ void __launch_bounds__(256) k_closest_keys(const __grid_constant__ DS
 	idx[k] = (unsigned)k;
 }
 
-// perm: NULL, or the order in which the queue's rays are taken (k_shadow_keys + radix sort); n = rays in the queue
+// perm: NULL, or the order in which the queue's rays are taken (k_shadow_keys + radix sort); n = rays in the queue.
+//
+// Shadow cache (phase 1 / 2, sorted launches only).  srsAttenuation is exactly 0 as soon as ONE entered non-transmissive
+// surface lies at t <= 0.49 D (any t for a directional light) - the any-hit argument of rt_shadow.cuh, which holds whatever
+// else the ray meets.  In (light, origin cell) order neighbouring rays are mostly blocked by the same object, so:
+//   phase 1: every 2^gs-th ray of the sorted order (the leaders) is walked; the candidate that settled it is written to occ[]
+//   phase 2: the other rays first test their leader's occluder alone (cand_test: the reference's box pretest, object-space
+//            ray and intersectLocalList of that one primitive); blocked -> done, nothing to add; else the ordinary walk.
+// phase 0: no cache (unsorted small rounds).
+struct ShadowSide; // rt_scan.cuh
+__device__ unsigned cand_test(const DScene& S, const d3& o, const d3& d, const rt_light& Lt, unsigned obj, unsigned pos);
+#define RT_OCC_NONE (~0ull)
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt,
-                                                                                const unsigned* __restrict__ perm, int sparse)
+                                                                                const unsigned* __restrict__ perm, int sparse, int phase, int gs, unsigned long long* occ)
 {
 	const long long t0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
 	if (t0 & ((1ll << sparse) - 1)) return; // one ray per 2^sparse lanes in rounds too small to fill the GPU (see k_wave_closest)
-	const long long k0 = t0 >> sparse;
+	long long k0 = t0 >> sparse;
+	if (phase == 1) k0 <<= gs;                                   // leaders only
+	else if (phase == 2 && (k0 & ((1ll << gs) - 1)) == 0) return; // the leaders are done
 	long long n = (long long)cnt->n_shadow[parity];
 	if (n > SQ.cap) n = SQ.cap;
 	if (k0 >= n) return;
 	const long long k = perm ? (long long)perm[k0] : k0;
 	const d3 ro = SQ.load_v(0, k), rd = SQ.load_v(3, k);
 	const rt_light& Lt = S.lights[SQ.i[SQ.cap + k]];
+	if (phase == 2) {
+		const unsigned long long c = occ[k0 >> gs];
+		if (c != RT_OCC_NONE && cand_test(S, ro, rd, Lt, (unsigned)(c >> 32), (unsigned)c)) return; // blocked by the leader's occluder: contributes 0
+	}
 	ShadowState st;
 	SBuf B;
 	TravClosest unused;
@@ -474,6 +491,15 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 		shadow_pass_reset(st, B);
 		traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B);
 		if (shadow_walk(st, B, Lt, rd, A.prm)) break;
+	}
+	if (phase == 1) {
+		unsigned long long c = RT_OCC_NONE;
+		if (B.dead) {
+			const DItemBox& ib = S.sboxf[(unsigned)(B.dead_key >> 32)];
+			const unsigned pos = ib.type == RT_OBJ_TRIMESH ? (unsigned)S.meshes[S.objs[ib.obj].mesh].item_off + (unsigned)B.dead_key : 0xffffffffu;
+			c = ((unsigned long long)(unsigned)ib.obj << 32) | pos;
+		}
+		occ[k0 >> gs] = c;
 	}
 	accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
 }

@@ -47,6 +47,7 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
+	int occ_shift = 3;                     // shadow cache: one leader per 2^occ_shift rays of a sorted shadow launch (RT_B200_OCC; 0 = no cache)
 	bool sparse_small = true;              // RT_B200_SPARSE=0: small rounds are launched densely (32 rays per warp) like large ones
 	bool defer_long = false;               // RT_B200_DEFER=0: rays that exhaust the node budget are retried in their own round instead of the next one
 	bool sort_closest = true;              // RT_B200_SORTC=0: reflection / refraction rays are walked in queue order instead of (octant, origin cell) order
@@ -72,7 +73,7 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_OCC_A, B_OCC_B, B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
        B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
@@ -371,7 +372,17 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 				STAGE_ON(sstream, RT_STAGE_OTHER, k_shadow_keys<<<blocks_for(ns, 256), 256, 0, sstream>>>(ctx->S, sq[par], ns, keys, idx));
 				STAGE_ON(sstream, RT_STAGE_OTHER, CK(cub::DeviceRadixSort::SortPairs(ctx->buf[bt], tmp_bytes, keys, keys + sq[par].cap, idx, idx + sq[par].cap, (int)ns, 0, 32, sstream)));
 				const int ssh = sparse_shift(ctx, ns);
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, ssh));
+				const int gs = (ssh == 0 && ns >= RT_SORT_MIN / 4) ? ctx->occ_shift : 0;
+				if (gs > 0) {
+					// shadow cache: the leaders (every 2^gs-th ray of the sorted order) first, then the rest against their leader's occluder
+					const long long n_lead = (ns + (1ll << gs) - 1) >> gs;
+					const int bo = par ? B_OCC_B : B_OCC_A;
+					if ((st = ensure(ctx, bo, (size_t)((sq[par].cap >> gs) + 1) * sizeof(unsigned long long))) != RT_OK) return st;
+					unsigned long long* occ = (unsigned long long*)ctx->buf[bo];
+					STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(n_lead, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, 0, 1, gs, occ));
+					STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, 0, 2, gs, occ));
+				} else
+					STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, ssh, 0, 0, nullptr));
 			}
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		} else if (L > 0) {
@@ -390,7 +401,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 				// the rays that met a transmissive / far-half surface (a few percent): the complete walk, persistent grid over the list
 				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow_list<<<(unsigned)ctx->sm_count * RT_SHADOW_MINB, RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], CQ));
 			} else
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for((m * L) << sparse_shift(ctx, m * L), RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr, sparse_shift(ctx, m * L)));
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for((m * L) << sparse_shift(ctx, m * L), RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr, sparse_shift(ctx, m * L), 0, 0, nullptr));
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
@@ -502,6 +513,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_DEFER")) ctx->defer_long = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SPARSE")) ctx->sparse_small = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_OCC")) { const int v = atoi(e); if (v >= 0 && v <= 8) ctx->occ_shift = v; }
 	if (const char* e = getenv("RT_B200_SHADOW")) ctx->shadow_mode = !strcmp(e, "one") ? 0 : (!strcmp(e, "split") ? 1 : 2);
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs

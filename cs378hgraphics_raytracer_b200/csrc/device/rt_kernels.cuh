@@ -74,8 +74,6 @@ __device__ __forceinline__ bool grid_sample(const PoolArgs& A, long long sample,
 } // namespace rtd
 #include "rt_pool.cuh"
 #include "rt_wave.cuh"
-#include "rt_scan.cuh"
-#include "rt_shadow_wb.cuh"
 namespace rtd {
 
 // ---- Scene::intersect for caller-supplied rays (rt_trace_rays hits) ---------------------------

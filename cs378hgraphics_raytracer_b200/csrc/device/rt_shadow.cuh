@@ -37,7 +37,6 @@ struct SBuf {
 	unsigned long long floor_key;
 	double min_dropped; // smallest t that was dropped for lack of space
 	double sure_t;      // an entered opaque surface at t <= sure_t makes the result exactly 0 (see sbuf_add)
-	unsigned long long dead_key; // candidate key (scene rank << 32 | mesh item / sub-hit) of the surface that settled it
 	bool dead;          // such a surface was found: the walk can stop, srsAttenuation returns dvec3(0)
 };
 
@@ -58,7 +57,7 @@ RT_COLD void sbuf_add(SBuf& B, double t, unsigned long long key, bool inside, bo
 	// before that surface (light.cpp:47-48) returns 0, and so does the surface itself.  So a
 	// non-transmissive entry at t <= sure_t (0.49 D, or infinity) settles the result whatever else
 	// the ray meets: no need to collect the hits in front of it.
-	if (term && !inside && t <= B.sure_t) { B.dead = true; B.cut = t; B.dead_key = key; return; }
+	if (term && !inside && t <= B.sure_t) { B.dead = true; B.cut = t; return; }
 	int pos = B.n;
 	while (pos > 0 && key_less(t, key, B.h[pos - 1].t, B.h[pos - 1].key)) pos--;
 	if (B.n == RT_SHADOW_K) {

@@ -24,8 +24,7 @@
 
 namespace rtd {
 
-enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1,
-       TRAV_SCAN = 2 }; // candidate listing for the split shadow stage (rt_scan.cuh): no primitive is tested during the walk
+enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1 };
 
 // Work counters for the cost model (scenes/cost_model.py): host build of tests/hostsim only.
 #if defined(RT_COUNT_WORK) && !defined(__CUDACC__)
@@ -204,7 +203,6 @@ struct Walk {
 	d3 o, d;             // the ray in the current space (world at level 0, the mesh's object space at level 1)
 	RayInv I;            // its double-precision inverse
 	double lim;          // best t so far / shadow cut, current space
-	double lim0;         // TRAV_SCAN: the fixed world-space limit of the listing walk
 	MeshVisit V;
 	const DNode2* nodes; // double images of the current tree's nodes
 	const DTri* tris;    // the current mesh's triangles
@@ -223,7 +221,7 @@ RT_COLD int walk_begin(const DScene& S, Walk& W, RayF& F, float& limf)
 	make_inv(W.I, F, W.o, W.d, W.prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
 	W.nodes = S.snodes2;
 	W.tris = S.tris;
-	W.lim = W.mode == TRAV_CLOSEST ? RT_T_INF : (W.mode == TRAV_SHADOW ? W.B->cut : W.lim0);
+	W.lim = W.mode == TRAV_CLOSEST ? RT_T_INF : W.B->cut;
 	limf = f_up(W.lim);
 	W.V.len = 1.0;
 	W.V.obj = -1;
@@ -380,7 +378,7 @@ template <int FIXED_MODE> RT_COLD void walk_mesh_exit(const DScene& S, Walk& W, 
 {
 	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : W.mode;
 	const MeshVisit& V = W.V;
-	TravClosest& C = *W.C; // (not dereferenced by the other modes)
+	TravClosest& C = *W.C;
 	if (mode == TRAV_CLOSEST && V.have) {
 		const double t = V.best_t / V.len;
 		if (!C.have || t < C.best_t || (t == C.best_t && V.rank < C.best_rank)) {
@@ -398,7 +396,7 @@ template <int FIXED_MODE> RT_COLD void walk_mesh_exit(const DScene& S, Walk& W, 
 	W.nodes = S.snodes2;
 	nodesf = S.snodes2f;
 	level = 0;
-	W.lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : (mode == TRAV_SHADOW ? W.B->cut : W.lim0);
+	W.lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : W.B->cut;
 	limf = f_up(W.lim);
 }
 

@@ -26,13 +26,6 @@
 
 namespace rtd {
 
-// A ray that exhausts its node budget does not hold up its round: k_wave_closest marks its hit record RT_T_DEFERRED, k_wave_shade
-// copies the ray unchanged into the next round's queue with this bit set, and there it is walked with 16 x the budget at the
-// front of the launch, beside that round's ordinary rays.  A frame then pays the tail of its longest closest-hit walks once,
-// in its last round, instead of once per recursion level (what limits tile-parallel scaling: the tails do not shrink with
-// the partition).  The winner of a walk does not depend on when it is walked, and a deferred ray is counted when it is shaded.
-#define META_DEFERRED (1 << 16)
-#define RT_T_DEFERRED (-2.0)
 enum { KIND_DEAD = 7 }; // a primary slot outside the image (edge tiles): skipped by every stage
 
 #define RT_WAVE_THREADS 128
@@ -78,7 +71,6 @@ struct WaveCounters {
 	unsigned long long heavy_cursor; // next heavy ray to be taken by a warp
 	unsigned long long n_retry;      // rays that exhausted the FIRST budget (k_wave_closest); k_wave_closest_retry walks them
 	                                 // again with a larger one and only its leftovers (n_heavy) go to the cooperative kernel
-	unsigned long long n_deferred;   // rays that exhausted the first budget and were put off to the next round (META_DEFERRED)
 	unsigned long long n_shadow[2];  // per round parity: the shadow rays of round r are still being
 	                                 // walked (second stream) while round r+1 fills the other queue
 };
@@ -138,8 +130,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 // and refraction rays arrive in the order their parents were shaded; sorted by direction octant and origin cell, the rays
 // of a warp walk the same subtrees).  Hit records stay indexed by queue slot, so the shade stage does not care.
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
-                                                                                    int budget, int* retry, unsigned long long* n_retry, const unsigned* __restrict__ perm, long long n_perm,
-                                                                                    unsigned long long* n_deferred, int sparse)
+                                                                                    int budget, int* retry, unsigned long long* n_retry, const unsigned* __restrict__ perm, long long n_perm, int sparse)
 {
 	// sparse > 0 (a round too small to fill the GPU): one ray per 2^sparse lanes.  A warp's time is the SUM of the divergent
 	// paths of its rays, a few lanes at a time; with fewer rays per warp and more warps the launch ends sooner, and the lanes
@@ -162,13 +153,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_clos
 	SBuf unused;
 	unused.n = 0;
 	unused.cut = RT_T_INF;
-	const bool second_try = (meta & META_DEFERRED) != 0;
-	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, second_try ? budget * 16 : budget)) {
-		if (n_deferred && !second_try) { // put off to the next round (n_deferred == NULL: deferral is off)
-			H.t[k] = RT_T_DEFERRED;
-			atomicAdd(n_deferred, 1ull);
-			return;
-		}
+	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, budget)) {
 		retry[atomicAdd(n_retry, 1ull)] = (int)k; // k_wave_closest_retry (or, with a forced budget, the cooperative kernel) redoes this ray
 		return;
 	}
@@ -269,9 +254,6 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 	MatEval me;
 	Hit h;
 	d3 w = mk3(0, 0, 0), hitP = mk3(0, 0, 0), rd = mk3(0, 0, 1);
-	// a ray whose walk was put off: it travels to the next round as it is, uncounted and unshaded
-	const bool deferred = live && H.t[k] == RT_T_DEFERRED;
-	if (deferred) live = false;
 	if (live) {
 		const int kind = (meta >> 12) & 15;
 		const d3 ro = Q.load_v(0, q);
@@ -307,19 +289,6 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 			Nxt.store_v(6, s, kid[c].weight);
 			Nxt.store_v(9, s, kid[c].att_kt);
 			Nxt.store_meta(s, sample, pack_meta(kid[c].depth, kid[c].att_mode, kid[c].kind, 0));
-		}
-	}
-	{
-		const long long s = wave_reserve(deferred, lt_mask, &cnt->n_children);
-		if (s >= 0) {
-			if (s >= Nxt.cap) overflow = 1;
-			else {
-				Nxt.store_v(0, s, Q.load_v(0, q));
-				Nxt.store_v(3, s, Q.load_v(3, q));
-				Nxt.store_v(6, s, Q.load_v(6, q));
-				Nxt.store_v(9, s, Q.load_v(9, q));
-				Nxt.store_meta(s, sample, meta | META_DEFERRED);
-			}
 		}
 	}
 	// one shadow ray per light (Material::shade's loop, material.cpp:50-66), light by light so
@@ -452,36 +421,19 @@ __global__ void __launch_bounds__(256) k_closest_keys(const __grid_constant__ DS
 	idx[k] = (unsigned)k;
 }
 
-// perm: NULL, or the order in which the queue's rays are taken (k_shadow_keys + radix sort); n = rays in the queue.
-//
-// Shadow cache (phase 1 / 2, sorted launches only).  srsAttenuation is exactly 0 as soon as ONE entered non-transmissive
-// surface lies at t <= 0.49 D (any t for a directional light) - the any-hit argument of rt_shadow.cuh, which holds whatever
-// else the ray meets.  In (light, origin cell) order neighbouring rays are mostly blocked by the same object, so:
-//   phase 1: every 2^gs-th ray of the sorted order (the leaders) is walked; the candidate that settled it is written to occ[]
-//   phase 2: the other rays first test their leader's occluder alone (cand_test: the reference's box pretest, object-space
-//            ray and intersectLocalList of that one primitive); blocked -> done, nothing to add; else the ordinary walk.
-// phase 0: no cache (unsorted small rounds).
-struct ShadowSide; // rt_scan.cuh
-__device__ unsigned cand_test(const DScene& S, const d3& o, const d3& d, const rt_light& Lt, unsigned obj, unsigned pos);
-#define RT_OCC_NONE (~0ull)
+// perm: NULL, or the order in which the queue's rays are taken (k_shadow_keys + radix sort).
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt,
-                                                                                const unsigned* __restrict__ perm, int sparse, int phase, int gs, unsigned long long* occ)
+                                                                                const unsigned* __restrict__ perm, int sparse)
 {
 	const long long t0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
 	if (t0 & ((1ll << sparse) - 1)) return; // one ray per 2^sparse lanes in rounds too small to fill the GPU (see k_wave_closest)
-	long long k0 = t0 >> sparse;
-	if (phase == 1) k0 <<= gs;                                   // leaders only
-	else if (phase == 2 && (k0 & ((1ll << gs) - 1)) == 0) return; // the leaders are done
+	const long long k0 = t0 >> sparse;
 	long long n = (long long)cnt->n_shadow[parity];
 	if (n > SQ.cap) n = SQ.cap;
 	if (k0 >= n) return;
 	const long long k = perm ? (long long)perm[k0] : k0;
 	const d3 ro = SQ.load_v(0, k), rd = SQ.load_v(3, k);
 	const rt_light& Lt = S.lights[SQ.i[SQ.cap + k]];
-	if (phase == 2) {
-		const unsigned long long c = occ[k0 >> gs];
-		if (c != RT_OCC_NONE && cand_test(S, ro, rd, Lt, (unsigned)(c >> 32), (unsigned)c)) return; // blocked by the leader's occluder: contributes 0
-	}
 	ShadowState st;
 	SBuf B;
 	TravClosest unused;
@@ -491,15 +443,6 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 		shadow_pass_reset(st, B);
 		traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B);
 		if (shadow_walk(st, B, Lt, rd, A.prm)) break;
-	}
-	if (phase == 1) {
-		unsigned long long c = RT_OCC_NONE;
-		if (B.dead) {
-			const DItemBox& ib = S.sboxf[(unsigned)(B.dead_key >> 32)];
-			const unsigned pos = ib.type == RT_OBJ_TRIMESH ? (unsigned)S.meshes[S.objs[ib.obj].mesh].item_off + (unsigned)B.dead_key : 0xffffffffu;
-			c = ((unsigned long long)(unsigned)ib.obj << 32) | pos;
-		}
-		occ[k0 >> gs] = c;
 	}
 	accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
 }

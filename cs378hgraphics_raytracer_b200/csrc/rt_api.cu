@@ -47,16 +47,9 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
-	int occ_shift = 3;                     // shadow cache: one leader per 2^occ_shift rays of a sorted shadow launch (RT_B200_OCC; 0 = no cache)
 	bool sparse_small = true;              // RT_B200_SPARSE=0: small rounds are launched densely (32 rays per warp) like large ones
-	bool defer_long = false;               // RT_B200_DEFER=0: rays that exhaust the node budget are retried in their own round instead of the next one
 	bool sort_closest = true;              // RT_B200_SORTC=0: reflection / refraction rays are walked in queue order instead of (octant, origin cell) order
 	bool sort_shadow = true;               // RT_B200_SORT=0: shadow rays are walked in queue order instead of (light, origin cell) order
-	int shadow_mode = 0;                   // how a round's shadow rays are walked (RT_B200_SHADOW=one|split|wb):
-	                                       //   0 one kernel, one thread per ray, candidates tested where they are met (k_wave_shadow)
-	                                       //   1 listing walk + per-kind candidate kernels (device/rt_scan.cuh): measured slower, kept for A/B
-	                                       //   2 one walk kernel with the candidates batched per warp and primitive kind (device/rt_shadow_wb.cuh)
-	bool kind_present[6] = {false, false, false, false, false, false}; // primitive kinds of the uploaded scene (a queue and a launch per kind present)
 	unsigned long long rounds = 0;
 	uint8_t* stage = nullptr;              // page-locked staging of rt_render_tiles' packed tiles
 	size_t stage_bytes = 0;
@@ -73,8 +66,7 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_OCC_A, B_OCC_B, B_SH_SIDE, B_SH_FLAGS, B_CQ0, B_CQ1, B_CQ2, B_CQ3, B_CQ4, B_CQ5, B_CQ_LIST, B_CQ_CNT,
-       B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_COUNT };
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -153,28 +145,6 @@ rt_status make_queue(rt_ctx* ctx, int bd, int bi, long long cap, int nd, RayQueu
 
 rt_status launch_pool(rt_ctx* ctx, PoolArgs& A);
 
-// Queues of the split shadow stage for up to `rays` shadow rays per round: three candidates per ray for the
-// common analytic kinds, four leaf triangles; a ray whose candidate finds its queue full takes the complete walk.
-rt_status make_cand_queues(rt_ctx* ctx, long long rays, CandQueues& Q)
-{
-	static const int mult[CQ_KINDS] = {3, 3, 1, 3, 1, 4};
-	rt_status st;
-	if ((st = ensure(ctx, B_SH_SIDE, (size_t)rays * sizeof(ShadowSide))) != RT_OK) return st;
-	if ((st = ensure(ctx, B_SH_FLAGS, (size_t)rays * sizeof(unsigned))) != RT_OK) return st;
-	if ((st = ensure(ctx, B_CQ_LIST, (size_t)rays * sizeof(int))) != RT_OK) return st;
-	if ((st = ensure(ctx, B_CQ_CNT, 64)) != RT_OK) return st;
-	for (int k = 0; k < CQ_KINDS; k++) {
-		Q.cap[k] = ctx->kind_present[k] ? (unsigned long long)rays * mult[k] : 0ull;
-		if ((st = ensure(ctx, B_CQ0 + k, (size_t)Q.cap[k] * (k == RT_OBJ_TRIMESH ? sizeof(uint4) : sizeof(uint2)))) != RT_OK) return st;
-		if (k == RT_OBJ_TRIMESH) Q.tri = (uint4*)ctx->buf[B_CQ0 + k];
-		else Q.q[k] = (uint2*)ctx->buf[B_CQ0 + k];
-	}
-	Q.count = (unsigned long long*)ctx->buf[B_CQ_CNT];
-	Q.n_complex = Q.count + CQ_KINDS;
-	Q.complex_list = (int*)ctx->buf[B_CQ_LIST];
-	return RT_OK;
-}
-
 cudaEvent_t next_event(rt_ctx* ctx)
 {
 	if (ctx->ev_used == ctx->ev_pool.size()) {
@@ -195,26 +165,6 @@ cudaEvent_t next_event(rt_ctx* ctx)
 	} while (0)
 #define STAGE(id, ...) STAGE_ON(ctx->stream, id, __VA_ARGS__)
 
-// One round's shadow rays through the split stage (device/rt_scan.cuh): listing walk, one candidate kernel per
-// primitive kind present in the scene, resolve, and the complete walk for what is left.
-rt_status launch_shadow_split(rt_ctx* ctx, const PoolArgs& A, const RayQueue& SQ, int par, WaveCounters* cnt, long long max_rays, const CandQueues& Q, cudaStream_t s)
-{
-	ShadowSide* side = (ShadowSide*)ctx->buf[B_SH_SIDE];
-	unsigned* flags = (unsigned*)ctx->buf[B_SH_FLAGS];
-	CK(cudaMemsetAsync(Q.count, 0, 64, s));
-	STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_scan<<<blocks_for(max_rays, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, s>>>(ctx->S, SQ, par, cnt, side, flags, Q));
-	const unsigned pgrid = (unsigned)ctx->sm_count * 8u; // persistent grids over the device-side counts
-	if (ctx->kind_present[RT_OBJ_SPHERE]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_SPHERE><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
-	if (ctx->kind_present[RT_OBJ_BOX]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_BOX><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
-	if (ctx->kind_present[RT_OBJ_SQUARE]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_SQUARE><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
-	if (ctx->kind_present[RT_OBJ_CYLINDER]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_CYLINDER><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
-	if (ctx->kind_present[RT_OBJ_CONE]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_CONE><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
-	if (ctx->kind_present[RT_OBJ_TRIMESH]) STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_cand<RT_OBJ_TRIMESH><<<pgrid, RT_CAND_THREADS, 0, s>>>(ctx->S, SQ, side, flags, Q));
-	STAGE_ON(s, RT_STAGE_SHADOW, k_shadow_resolve<<<blocks_for(max_rays, 256), 256, 0, s>>>(A, SQ, par, cnt, flags, Q));
-	STAGE_ON(s, RT_STAGE_SHADOW, k_wave_shadow_list<<<(unsigned)ctx->sm_count * RT_SHADOW_MINB, RT_TRACE_THREADS, 0, s>>>(ctx->S, A, SQ, Q));
-	return RT_OK;
-}
-
 // The trace loop over n_slots primary-ray slots as a streaming wavefront (device/rt_wave.cuh).
 rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 {
@@ -227,8 +177,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	// bytes per ray of the round, so the width is what a quarter of the device memory holds, at most 32 Mi.
 	long long W = ctx->wave_width;
 	if (W <= 0) {
-		// + per shadow ray of the split shadow stage: side record, flags, list entry and the candidate queues (launch_shadow_split)
-		const size_t per_ray = 4 * 104 + 2 * (size_t)(L > 0 ? L : 1) * 80 + 24 + (ctx->shadow_mode == 1 ? (size_t)(L > 0 ? L : 1) * 200 : (ctx->shadow_mode == 2 ? (size_t)(L > 0 ? L : 1) * 4 : 0));
+		const size_t per_ray = 4 * 104 + 2 * (size_t)(L > 0 ? L : 1) * 80 + 24 + (size_t)(L > 0 ? L : 1) * 16; // 16: sort keys and permutation
 		W = (long long)(ctx->queue_budget / per_ray) / 1024 * 1024;
 		// the spill stack (allocated only if a round ever has more than W children) may take another half of the memory
 		const long long spill_fit = (long long)(2 * ctx->queue_budget / (((size_t)(A.depth < 30 ? A.depth : 30) + 2) * 104)) / 1024 * 1024;
@@ -247,20 +196,6 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	if ((st = make_queue(ctx, B_SQ2_D, B_SQ2_I, W * (L > 0 ? L : 1), 9, sq[1])) != RT_OK) return st;
 	// per-stage profiling wants clean kernel times: no overlap then
 	const bool overlap = ctx->overlap && !ctx->profile;
-	const bool split = ctx->shadow_mode == 1 && L > 0;
-	const bool wb = ctx->shadow_mode == 2 && L > 0 && ctx->S.n_objs < (1 << 27); // the queues pack (object, owner lane) into 32 bits
-	CandQueues CQ;
-	std::memset(&CQ, 0, sizeof(CQ));
-	if (split && (st = make_cand_queues(ctx, W * L, CQ)) != RT_OK) return st;
-	unsigned kind_mask = 0;
-	if (wb) { // only the list of "complex" rays and its counter
-		if ((st = ensure(ctx, B_CQ_LIST, (size_t)W * L * sizeof(int))) != RT_OK) return st;
-		if ((st = ensure(ctx, B_CQ_CNT, 64)) != RT_OK) return st;
-		CQ.count = (unsigned long long*)ctx->buf[B_CQ_CNT];
-		CQ.n_complex = CQ.count + CQ_KINDS;
-		CQ.complex_list = (int*)ctx->buf[B_CQ_LIST];
-		for (int k = 0; k < CQ_KINDS; k++) kind_mask |= ctx->kind_present[k] ? 1u << k : 0u;
-	}
 	bool shadow_pending[2] = {false, false};
 	long long round = 0;
 	if ((st = ensure(ctx, B_WH_T, (size_t)W * sizeof(double))) != RT_OK) return st;
@@ -309,7 +244,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		}
 		if (m == 0) break;
 		const int par = (int)(round & 1);
-		CK(cudaMemsetAsync(&cnt->n_children, 0, 5 * sizeof(unsigned long long), ctx->stream)); // children, heavy, cursor, retry, deferred
+		CK(cudaMemsetAsync(&cnt->n_children, 0, 4 * sizeof(unsigned long long), ctx->stream)); // children, heavy, cursor, retry
 		// a forced budget (RT_B200_BUDGET, the tests) sends its leftovers straight to the cooperative kernel
 		const bool second = ctx->budget_auto && ctx->walk_budget > 0;
 		const unsigned* cperm = nullptr;
@@ -327,8 +262,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		} else n_kids = 0;
 		const int csh = sparse_shift(ctx, m);
 		STAGE(RT_STAGE_CLOSEST, k_wave_closest<<<blocks_for(m << csh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, ctx->stream>>>(ctx->S, cur, base, m, H, ctx->walk_budget,
-		                                                                                                                second ? retry : heavy, second ? &cnt->n_retry : &cnt->n_heavy, cperm, n_kids,
-		                                                                                                                (second && ctx->defer_long) ? &cnt->n_deferred : nullptr, csh));
+		                                                                                                                second ? retry : heavy, second ? &cnt->n_retry : &cnt->n_heavy, cperm, n_kids, csh));
 		if (second) {
 			// second chance with 8 x the budget: grid for 1/32 of the round (a grid-stride loop takes whatever there is)
 			const unsigned rblocks = blocks_for((m + 31) / 32, RT_TRACE_THREADS);
@@ -342,16 +276,16 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		shadow_pending[par] = false;
 		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
-		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry, deferred, shadow rays [2]
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry, shadow rays [2]
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		// Large rounds: the shadow rays are walked in (light, origin cell) order.  The radix sort needs the number of rays on
 		// the host, which arrives with the counters the host waits for anyway - so the wait moves in front of the launch.
-		const bool sorted = L > 0 && !split && !wb && ctx->sort_shadow && m * L >= RT_SORT_MIN;
+		const bool sorted = L > 0 && ctx->sort_shadow && m * L >= RT_SORT_MIN;
 		bool synced = false;
 		if (sorted) {
 			CK(cudaEventSynchronize(ctx->ev_round));
 			synced = true;
-			long long ns = (long long)ctx->pinned[5 + par];
+			long long ns = (long long)ctx->pinned[4 + par];
 			if (ns > sq[par].cap) ns = sq[par].cap;
 			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
 			if (overlap) {
@@ -372,36 +306,18 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 				STAGE_ON(sstream, RT_STAGE_OTHER, k_shadow_keys<<<blocks_for(ns, 256), 256, 0, sstream>>>(ctx->S, sq[par], ns, keys, idx));
 				STAGE_ON(sstream, RT_STAGE_OTHER, CK(cub::DeviceRadixSort::SortPairs(ctx->buf[bt], tmp_bytes, keys, keys + sq[par].cap, idx, idx + sq[par].cap, (int)ns, 0, 32, sstream)));
 				const int ssh = sparse_shift(ctx, ns);
-				const int gs = (ssh == 0 && ns >= RT_SORT_MIN / 4) ? ctx->occ_shift : 0;
-				if (gs > 0) {
-					// shadow cache: the leaders (every 2^gs-th ray of the sorted order) first, then the rest against their leader's occluder
-					const long long n_lead = (ns + (1ll << gs) - 1) >> gs;
-					const int bo = par ? B_OCC_B : B_OCC_A;
-					if ((st = ensure(ctx, bo, (size_t)((sq[par].cap >> gs) + 1) * sizeof(unsigned long long))) != RT_OK) return st;
-					unsigned long long* occ = (unsigned long long*)ctx->buf[bo];
-					STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(n_lead, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, 0, 1, gs, occ));
-					STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, 0, 2, gs, occ));
-				} else
-					STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, ssh, 0, 0, nullptr));
+				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, ssh));
 			}
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		} else if (L > 0) {
-			// the split stage's queues are shared by both parities: its pipelines follow one another on one stream
-			cudaStream_t sstream = overlap ? ctx->stream2[(split || wb) ? 0 : par] : ctx->stream;
+			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
 			if (overlap) {
 				CK(cudaEventRecord(ctx->ev_shade[par], ctx->stream));
 				CK(cudaStreamWaitEvent(sstream, ctx->ev_shade[par], 0));
 			}
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
-			if (split) {
-				if ((st = launch_shadow_split(ctx, A, sq[par], par, cnt, m * L, CQ, sstream)) != RT_OK) return st;
-			} else if (wb) {
-				CK(cudaMemsetAsync(CQ.count, 0, 64, sstream));
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow_wb<<<blocks_for(m * L, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, CQ, kind_mask));
-				// the rays that met a transmissive / far-half surface (a few percent): the complete walk, persistent grid over the list
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow_list<<<(unsigned)ctx->sm_count * RT_SHADOW_MINB, RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], CQ));
-			} else
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for((m * L) << sparse_shift(ctx, m * L), RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr, sparse_shift(ctx, m * L), 0, 0, nullptr));
+			const int ssh = sparse_shift(ctx, m * L);
+			STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for((m * L) << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr, ssh));
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
@@ -413,18 +329,12 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		// path gives the same hit, so this only moves work between the two kernels.
 		// (pinned[3]: the rays that ran out of the first budget.  A round walked before the budget has grown is not
 		// lost: its leftovers get a second single-thread chance, k_wave_closest_retry.)
-		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)(ctx->pinned[3] + ctx->pinned[4]) * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
+		if (ctx->budget_auto && ctx->walk_budget > 0 && m >= 4096 && (long long)ctx->pinned[3] * 64 > m && ctx->walk_budget < 16384) ctx->walk_budget *= 2;
 		round++;
 		const RayQueue tmp = cur;
 		cur = nxt;
 		nxt = tmp;
 		ctx->rounds++;
-	}
-	if ((split || wb) && getenv("RT_B200_DEBUG")) {
-		unsigned long long h[8];
-		cudaDeviceSynchronize();
-		cudaMemcpy(h, CQ.count, 64, cudaMemcpyDeviceToHost);
-		fprintf(stderr, "[rt_b200] last round: candidates sphere %llu box %llu square %llu cylinder %llu cone %llu triangle %llu, complex rays %llu\n", h[0], h[1], h[2], h[3], h[4], h[5], h[6]);
 	}
 	// everything that follows on the main stream (resolve kernels, the frame copy) needs the last shadow rays
 	for (int par = 0; par < 2; par++)
@@ -511,10 +421,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_POOL")) ctx->use_pool = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
-	if (const char* e = getenv("RT_B200_DEFER")) ctx->defer_long = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SPARSE")) ctx->sparse_small = atoi(e) != 0;
-	if (const char* e = getenv("RT_B200_OCC")) { const int v = atoi(e); if (v >= 0 && v <= 8) ctx->occ_shift = v; }
-	if (const char* e = getenv("RT_B200_SHADOW")) ctx->shadow_mode = !strcmp(e, "one") ? 0 : (!strcmp(e, "split") ? 1 : 2);
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;
@@ -633,11 +540,8 @@ static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes,
 	}
 	{
 		const rt_object* objs = A.ptr<rt_object>(RT_SEC_OBJECTS);
-		for (int k = 0; k < 6; k++) ctx->kind_present[k] = false;
-		for (uint64_t k = 0; k < A.count(RT_SEC_OBJECTS); k++) {
+		for (uint64_t k = 0; k < A.count(RT_SEC_OBJECTS); k++)
 			if (objs[k].type < RT_OBJ_SPHERE || objs[k].type > RT_OBJ_TRIMESH) { ctx->error = "unknown object type"; return RT_ERR_ARG; }
-			ctx->kind_present[objs[k].type] = true;
-		}
 	}
 	const long long n_snodes = (long long)A.count(RT_SEC_SCENE_NODES), n_mnodes = (long long)A.count(RT_SEC_MESH_NODES);
 	const long long n_mitems = (long long)A.count(RT_SEC_MESH_ITEMS), n_sitems = (long long)A.count(RT_SEC_SCENE_ITEMS);

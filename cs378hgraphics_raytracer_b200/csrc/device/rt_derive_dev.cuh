@@ -97,6 +97,26 @@ __global__ void __launch_bounds__(256) k_derive_itembox(const int32_t* sitems, l
 	out[k] = b;
 }
 
+// breadth-first top table of the scene tree (rt_scene.cuh: RT_REF_TOP); one thread, at most `cap` nodes
+__global__ void k_derive_top(const DNode2f* nodesf, int root, int cap, DNode2f* out, int* n_out)
+{
+	if (threadIdx.x || blockIdx.x) return;
+	int n = 0;
+	if (root >= 0 && cap > 0) {
+		out[0] = nodesf[root];
+		out[0].pad[0] = root;
+		n = 1;
+		for (int j = 0; j < n; j++) {
+			DNode2f nd = out[j];
+			if (nd.c0 >= 0 && n < cap) { out[n] = nodesf[nd.c0]; out[n].pad[0] = nd.c0; nd.c0 = RT_REF_TOP | n; n++; }
+			if (nd.c1 >= 0 && n < cap) { out[n] = nodesf[nd.c1]; out[n].pad[0] = nd.c1; nd.c1 = RT_REF_TOP | n; n++; }
+			out[j].c0 = nd.c0;
+			out[j].c1 = nd.c1;
+		}
+	}
+	*n_out = n;
+}
+
 __device__ __forceinline__ double dev_box_extent(const rt_node& n)
 {
 	double m = 1.0;

@@ -44,6 +44,13 @@ struct alignas(32) DItemBox {
 	int32_t obj;
 	int32_t type; // rt_object_type of obj: the split shadow stage queues candidates by primitive kind without reading the object
 };
+// Shared-memory staging of the scene tree's top (north star item 1; A/B in profiles/r2_variants.txt): the first RT_TOP_K internal
+// nodes in BREADTH-FIRST order (the arrays are pre-order, so the top levels are not contiguous) as a table of DNode2f whose child
+// references to other table entries carry RT_REF_TOP | table index; pad[0] = the node's index in snodes2 (for the double boxes).
+#ifndef RT_TOP_K
+#define RT_TOP_K 0 // 0 = off
+#endif
+#define RT_REF_TOP ((int32_t)0x40000000)
 #define RT_REF_MESH_EXIT ((int32_t)0x80000000)
 #define RT_REF_NONE ((int32_t)0x80000001)
 RT_HD int32_t leaf_ref(int32_t first, int32_t count) { return -(1 + ((first << 2) | count)); }
@@ -64,6 +71,9 @@ struct DScene {
 	const DNode2f* snodes2f; // float images, same indexing
 	const DNode2f* mnodes2f;
 	const DItemBox* sboxf;   // per scene leaf item
+	const DNode2f* stop;     // top table of the scene tree (RT_TOP_K entries, n_top used); see RT_REF_TOP
+	int32_t n_top;
+	int32_t pad_top_;
 	const DTree* mtrees; // per mesh
 	const rt_node* snodes;
 	const int32_t* sitems;

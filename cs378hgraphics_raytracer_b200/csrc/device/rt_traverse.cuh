@@ -408,7 +408,7 @@ template <int FIXED_MODE> RT_COLD void walk_mesh_exit(const DScene& S, Walk& W, 
 // All ways out of the loop are in the pop section: a second exit inside the node or leaf loops costs
 // the warp its reconvergence points (profiles/r1_variants.txt: 3x slower).
 template <bool PRUNE, int FIXED_MODE = -1>
-RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B, int budget = 0)
+RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B, int budget = 0, const DNode2f* top = nullptr)
 {
 	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : mode_arg;
 	RT_WORK_SCOPE(mode);
@@ -428,20 +428,22 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 	int sp = 0;
 	int cur = walk_begin(S, W, F, limf);
 	if (cur == RT_REF_NONE) return true;
+	if (RT_TOP_K > 0 && top && cur >= 0) cur = RT_REF_TOP; // the root is entry 0 of the staged table
 	bool done = true;
 	const bool limited = budget > 0;
 	for (;;) {
 		// ---- 1. internal nodes: test both children, go near, push far ---------------------------
 #pragma unroll 1
 		while (cur >= 0) {
-			const DNode2f nf = ld_node2f(nodesf + cur);
+			const bool staged = RT_TOP_K > 0 && (cur & RT_REF_TOP) != 0;
+			const DNode2f nf = staged ? top[cur & (RT_REF_TOP - 1)] : ld_node2f(nodesf + cur);
 			RT_CNT(nodes, mode);
 			budget--;
 			float e0, e1;
 			int r0 = boxf(nf.lo0, nf.hi0, F, e0);
 			int r1 = boxf(nf.lo1, nf.hi1, F, e1);
-			if (r0 == 2) { const StackEnt r = walk_resolve(W, cur, 0); r0 = r.ref; e0 = r.e; }
-			if (r1 == 2) { const StackEnt r = walk_resolve(W, cur, 1); r1 = r.ref; e1 = r.e; }
+			if (r0 == 2) { const StackEnt r = walk_resolve(W, staged ? nf.pad[0] : cur, 0); r0 = r.ref; e0 = r.e; }
+			if (r1 == 2) { const StackEnt r = walk_resolve(W, staged ? nf.pad[0] : cur, 1); r1 = r.ref; e1 = r.e; }
 			bool h0 = r0 != 0, h1 = r1 != 0;
 			if (prune) { h0 = h0 && !(e0 > limf); h1 = h1 && !(e1 > limf); }
 			if (h0 && h1) {

@@ -122,6 +122,22 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 	Q.store_meta(q, (int)smp, pack_meta(A.depth, 0, ok ? KIND_CAMERA : KIND_DEAD, 0));
 }
 
+// Per-block copy of the scene tree's top table into shared memory (rt_scene.cuh: RT_REF_TOP); every thread of the block takes
+// part, so this comes before any early return.  With RT_TOP_K == 0 (the default build) it compiles to nothing.
+#if RT_TOP_K > 0
+#define RT_STAGE_TOP(S, TOPVAR)                                                                          \
+	__shared__ DNode2f s_top_[RT_TOP_K];                                                                 \
+	{                                                                                                    \
+		const float4* src_ = reinterpret_cast<const float4*>((S).stop);                                  \
+		float4* dst_ = reinterpret_cast<float4*>(s_top_);                                                \
+		for (int i_ = threadIdx.x; i_ < (S).n_top * 4; i_ += blockDim.x) dst_[i_] = __ldg(src_ + i_);    \
+		__syncthreads();                                                                                 \
+	}                                                                                                    \
+	const DNode2f* TOPVAR = (S).n_top > 0 ? s_top_ : nullptr
+#else
+#define RT_STAGE_TOP(S, TOPVAR) const DNode2f* TOPVAR = nullptr
+#endif
+
 // ---- stage 1: Scene::intersect ----------------------------------------------------------------
 #ifndef RT_CLOSEST_MINB
 #define RT_CLOSEST_MINB 14 // 72 registers: the walk is latency bound, more resident warps beat fewer spills (profiles/r1_variants.txt)
@@ -132,6 +148,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_closest(const __grid_constant__ DScene S, const RayQueue Q, long long base, long long m, const HitQueue H,
                                                                                     int budget, int* retry, unsigned long long* n_retry, const unsigned* __restrict__ perm, long long n_perm, int sparse)
 {
+	RT_STAGE_TOP(S, top);
 	// sparse > 0 (a round too small to fill the GPU): one ray per 2^sparse lanes.  A warp's time is the SUM of the divergent
 	// paths of its rays, a few lanes at a time; with fewer rays per warp and more warps the launch ends sooner, and the lanes
 	// left idle would have had nothing to do anyway.
@@ -153,7 +170,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_CLOSEST_MINB) k_wave_clos
 	SBuf unused;
 	unused.n = 0;
 	unused.cut = RT_T_INF;
-	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, budget)) {
+	if (!traverse<true, TRAV_CLOSEST>(S, ro, rd, TRAV_CLOSEST, C, unused, budget, top)) {
 		retry[atomicAdd(n_retry, 1ull)] = (int)k; // k_wave_closest_retry (or, with a forced budget, the cooperative kernel) redoes this ray
 		return;
 	}
@@ -425,6 +442,7 @@ __global__ void __launch_bounds__(256) k_closest_keys(const __grid_constant__ DS
 __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt,
                                                                                 const unsigned* __restrict__ perm, int sparse)
 {
+	RT_STAGE_TOP(S, top);
 	const long long t0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
 	if (t0 & ((1ll << sparse) - 1)) return; // one ray per 2^sparse lanes in rounds too small to fill the GPU (see k_wave_closest)
 	const long long k0 = t0 >> sparse;
@@ -441,7 +459,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 	shadow_begin(st, B, Lt, ro);
 	for (;;) {
 		shadow_pass_reset(st, B);
-		traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B);
+		traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B, 0, top);
 		if (shadow_walk(st, B, Lt, rd, A.prm)) break;
 	}
 	accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);

@@ -66,7 +66,7 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_COUNT };
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_STOP, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -602,6 +602,18 @@ static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes,
 	S.snodes2f = (const DNode2f*)ctx->buf[B_SNODES2F];
 	S.mnodes2f = (const DNode2f*)ctx->buf[B_MNODES2F];
 	S.sboxf = (const DItemBox*)ctx->buf[B_SBOXF];
+	S.stop = nullptr;
+	S.n_top = 0;
+	S.pad_top_ = 0;
+	int* d_ntop = nullptr;
+	if (RT_TOP_K > 0 && n_snodes < (1ll << 30) && n_mnodes < (1ll << 30)) { // RT_REF_TOP must not collide with a node index
+		if ((st = ensure(ctx, B_STOP, (size_t)RT_TOP_K * sizeof(DNode2f) + 16)) != RT_OK) return st;
+		d_ntop = (int*)((uint8_t*)ctx->buf[B_STOP] + (size_t)RT_TOP_K * sizeof(DNode2f));
+		const rt_node& r0 = A.ptr<rt_node>(RT_SEC_SCENE_NODES)[0];
+		k_derive_top<<<1, 32, 0, ctx->stream>>>((const DNode2f*)ctx->buf[B_SNODES2F], r0.right >= 0 ? 0 : -1, RT_TOP_K, (DNode2f*)ctx->buf[B_STOP], d_ntop);
+		ctx->launches++;
+		S.stop = (const DNode2f*)ctx->buf[B_STOP];
+	}
 	S.mtrees = (const DTree*)ctx->buf[B_MTREES];
 	S.mesh_slack = (const double*)ctx->buf[B_MSLACK];
 	S.tris = (const DTri*)ctx->buf[B_TRIS];
@@ -621,6 +633,7 @@ static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes,
 	S.kt_unit = kt_all_unit(A.ptr<rt_material>(RT_SEC_MATERIALS), A.count(RT_SEC_MATERIALS));
 	S.pad_ = 0;
 	unsigned hflags[3];
+	if (d_ntop) CK(cudaMemcpyAsync(&S.n_top, d_ntop, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream)); // also: the caller may reuse `arena` on return
 	if (hflags[0]) { ctx->error = "invalid arena: index out of range (device check " + std::to_string(hflags[0]) + ")"; return RT_ERR_ARG; }

@@ -42,6 +42,9 @@ WORKLOADS = {
                params=dict(depth=5, aa_mode=1, aa_samples=4, use_cubemap=1), cubemap=512),
     "c4a": dict(name="C4 hitchcock stand-in 2048x2048, adaptive AA 4x4 thresh 0.01, cubemap, depth 5", gen=("hitchcock", 1.0), w=2048,
                 params=dict(depth=5, aa_mode=2, aa_samples=4, aa_thresh=0.01, use_cubemap=1), cubemap=512),
+    # -O c (adaptive termination) on two configurations: the mode that runs on the fused kernel k_trace_pool
+    "c1t": dict(name="C1 hitchcock stand-in 512x512, depth 5, adaptive termination 0.05", gen=("hitchcock", 1.0), w=512, params=dict(depth=5, aterm_thresh=0.05)),
+    "c3t": dict(name="C3 dragon stand-in 1920x1080, depth 5, adaptive termination 0.05", gen=("dragon", 1.0), w=1920, params=dict(depth=5, aterm_thresh=0.05)),
     "c5": dict(name="C5 synthetic 1M-primitive mixed scene 7680x4320, depth 8", gen=("mixed", 1.0), w=7680, params=dict(depth=8)),
 }
 SCENE_CACHE = os.environ.get("RT_SCENE_CACHE", os.path.join(tempfile.gettempdir(), "rt_b200_scenes"))

@@ -565,3 +565,26 @@ def test_multi_gpu_abi(rtlib, ctx, scene_dir):
         rtlib.MultiContext([0, 0])  # one rank per GPU
     with pytest.raises(rtlib.RtError):
         rtlib.MultiContext([n_dev])
+
+
+@pytest.mark.parametrize("scene", SCENES)
+@pytest.mark.parametrize("thresh", [0.05, 0.4])
+def test_adaptive_termination_all_scenes(rtlib, oracle_mod, ctx, scene_path, scene, thresh):
+    """-O c (traceUI->aTermSwitch, RayTracer.cpp:125 and light.cpp:48): recursion stops where the shaded colour's squared
+    length is below the threshold, shadow walks stop when the attenuation's is.  This mode needs the shadowed colour before it
+    recurses, so it runs on the fused persistent kernel (k_trace_pool) instead of the streaming wavefront: frames within the
+    tolerance and ray counts equal the reference's on every small scene, at a low and a high threshold."""
+    arena, orc = _load(rtlib, oracle_mod, ctx, scene_path(scene))
+    w = 160
+    h = oracle_mod.frame_height(w, orc.aspect)
+    p = rtlib.Params.default(depth=5, aterm_thresh=thresh)
+    ref_img, ref_st, _ = orc.render(p, w, h)
+    dev_img, dev_st = ctx.render(p, w, h)
+    d = oracle_mod.image_diff(ref_img, dev_img)
+    assert d["within1"] >= TOL_WITHIN1, d
+    for f in ("camera_rays", "reflection_rays", "refraction_rays", "shadow_rays"):
+        a, b = int(getattr(ref_st, f)), int(getattr(dev_st, f))
+        assert abs(a - b) <= max(2, 1e-3 * a), (f, a, b)
+    # and the switch really prunes: fewer secondary rays than without it (where the scene has any)
+    _, full_st = ctx.render(rtlib.Params.default(depth=5), w, h)
+    assert dev_st.reflection_rays + dev_st.refraction_rays <= full_st.reflection_rays + full_st.refraction_rays

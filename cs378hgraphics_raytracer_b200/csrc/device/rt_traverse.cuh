@@ -24,7 +24,8 @@
 
 namespace rtd {
 
-enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1 };
+enum { TRAV_CLOSEST = 0, TRAV_SHADOW = 1,
+       TRAV_ANYHIT = 2 }; // shadow query answered by classification only (AnyHit below): no hit list, no kt, no sorting
 
 // Work counters for the cost model (scenes/cost_model.py): host build of tests/hostsim only.
 #if defined(RT_COUNT_WORK) && !defined(__CUDACC__)
@@ -77,6 +78,117 @@ struct TravClosest {
 
 // world-space limit -> object space, inflated so rounding in the conversion can never cull a winner
 RT_HD double lim_to_local(double lim, double len) { return lim < RT_T_INF ? (lim * len) * (1.0 + 1e-9) + 1e-300 : RT_T_INF; }
+
+// TRAV_ANYHIT: Light::srsAttenuation (light.cpp:21-53) decided without its hit list wherever that is possible.
+//   SH_DEAD : some entered non-transmissive surface lies at t <= sure_t.  srsAttenuation is then exactly 0 whatever else the
+//             ray meets (the any-hit argument of rt_shadow.cuh: sbuf_add) - the walk stops at once.
+//   SH_OTHER: some other hit lies within the light's distance (a transmissive surface, a surface in the far half of the
+//             segment, an exit from an object the origin is inside of): the ray needs the complete sorted walk (TRAV_SHADOW).
+//   neither : nothing is hit before the light: the attenuation is exactly (1,1,1).
+// A second exact shortcut, for rays that start just INSIDE an opaque object (the shadow ray's origin is backed up along the view
+// ray, light.cpp:16-20, and may land under the surface it left): if the NEAREST hit of all is an exit (N.d > 0) from a medium
+// whose kt is exactly (0,0,0), at t <= sure_t, the sorted walk multiplies the attenuation by pow(0, t - 0) = 0 at its first step
+// (light.cpp:50; the limit check before it cannot fire at t <= 0.49 D) and the result is exactly 0.  "Nearest" must be strict -
+// a second hit at the same t would be processed with delta 0 somewhere - so the walk tracks t_x, the nearest such exit, and t_o,
+// the nearest hit of any other kind; beyond t_x nothing needs to be looked at any more (the pruning limit drops to t_x).
+enum { SH_DEAD = 1, SH_OTHER = 2,
+       SH_NEWLIM = 4 }; // t_x has dropped since the walk last looked: its pruning limit follows
+struct AnyHit {
+	double limit;  // hits beyond this cannot change the result (past a point light); the pruning limit of the walk
+	double sure_t; // 0.49 D for a point light, infinity for a directional one
+	double t_x;    // nearest exit from a kt = 0 medium at t <= sure_t
+	double t_o;    // nearest hit of any other kind
+	unsigned fl;
+	RT_HD double prune() const { return t_x < limit ? t_x : limit; }
+	RT_HD bool settled_by_exit() const { return t_x < t_o; } // (t_x finite: some such exit exists and is strictly nearest)
+};
+RT_HD void anyhit_classify(AnyHit& Y, double t, bool inside, bool trans, bool kt_zero)
+{
+	if (!(t <= Y.limit)) return;
+	if (!inside && !trans && t <= Y.sure_t) { Y.fl |= SH_DEAD; return; }
+	Y.fl |= SH_OTHER;
+	if (inside && kt_zero && t <= Y.sure_t) { if (t < Y.t_x) { Y.t_x = t; Y.fl |= SH_NEWLIM; } }
+	else if (t < Y.t_o) Y.t_o = t;
+}
+RT_HD bool kt_is_zero(const double* k) { return k[0] == 0.0 && k[1] == 0.0 && k[2] == 0.0; }
+// the hits of an analytic primitive (object space -> world), classified
+struct AnyEmit {
+	const DScene& S;
+	const rt_object& ob;
+	const d3& dw;
+	double len;
+	AnyHit& Y;
+	RT_HD void operator()(double tl, d3 Nl, d2 uv, int) const
+	{
+		if (Y.fl & SH_DEAD) return; // settled by an earlier hit of this primitive (its entry): the exit does not matter any more
+		const double t = tl / len;
+		if (!(t <= Y.limit)) return;
+		const d3 N = world_normal(S, ob, Nl, uv);
+		const rt_material& m = S.mats[ob.material];
+		const bool inside = dot(N, dw) > 0;
+		// kt lies on another cache line of the material record than the flags: read it for exits only
+		anyhit_classify(Y, t, inside, m.trans != 0, inside && m.tex[RT_KT] < 0 && kt_is_zero(m.k[RT_KT]));
+	}
+};
+RT_COLD void prim_anyhit(const DScene& S, const rt_object& ob, const LocalRay& L, const d3& dw, AnyHit& Y)
+{
+	const AnyEmit emit{S, ob, dw, L.len, Y};
+	switch (ob.type) {
+	case RT_OBJ_SPHERE: sphere_list(L.o, L.d, emit); break;
+	case RT_OBJ_BOX: box_list(L.o, L.d, emit); break;
+	case RT_OBJ_SQUARE: {
+		LocalHit h;
+		h.uv.x = h.uv.y = 0.0;
+		if (square_hit<true>(L.o, L.d, h)) emit(h.t, h.N, h.uv, 0);
+		break;
+	}
+	case RT_OBJ_CYLINDER: cylinder_list(L.o, L.d, emit); break;
+	case RT_OBJ_CONE: cone_list(L.o, L.d, ob.cone, ob.capped, emit); break;
+	default: break;
+	}
+}
+// a mesh face that the short triangle test reported hit: TrimeshFace::intersectLocal's normal (trimesh.cpp:146-174), classified
+RT_COLD void face_anyhit(const DScene& S, int obj, int pos, double len, const d3& o, const d3& d, const d3& dw, AnyHit& Y)
+{
+	const rt_object& ob = S.objs[obj];
+	const rt_mesh& M = S.meshes[ob.mesh];
+	const int fpos = (int)M.item_off + pos;
+	d3 bary;
+	double tl;
+	tri_hit<true>(S.tris[fpos], o, d, tl, bary);
+	const double t = tl / len;
+	if (!(t <= Y.limit)) return;
+	const rt_face& f = S.faces[M.face_off + S.mitems[fpos]];
+	d3 Nl;
+	if (M.vnorm_off >= 0) {
+		const double* n0 = S.vnormals + 3 * (M.vnorm_off + f.ids[0]);
+		const double* n1 = S.vnormals + 3 * (M.vnorm_off + f.ids[1]);
+		const double* n2 = S.vnormals + 3 * (M.vnorm_off + f.ids[2]);
+		Nl = normalize(mk3(n0[0] * bary.x + n1[0] * bary.y + n2[0] * bary.z,
+		                   n0[1] * bary.x + n1[1] * bary.y + n2[1] * bary.z,
+		                   n0[2] * bary.x + n1[2] * bary.y + n2[2] * bary.z));
+	} else {
+		Nl = ld3(f.normal);
+	}
+	const d3 N = normalize(mul33(ob.normi, Nl));
+	// eval_kt's `trans`: false for a mesh with per-vertex materials (the blended Material's flags are never set), else the object's
+	const bool inside = dot(N, dw) > 0;
+	bool trans = false, kt_zero = false;
+	if (!inside) {
+		trans = M.vmat_off >= 0 ? false : S.mats[ob.material].trans != 0;
+	} else if (M.vmat_off >= 0) { // kt = barycentric blend of the three vertex materials (eval_kt): zero iff the blend is
+		const rt_material& a = S.mats[S.vmats[M.vmat_off + f.ids[0]]];
+		const rt_material& b = S.mats[S.vmats[M.vmat_off + f.ids[1]]];
+		const rt_material& c = S.mats[S.vmats[M.vmat_off + f.ids[2]]];
+		const d3 kt = blend3(a.k[RT_KT], b.k[RT_KT], c.k[RT_KT], bary);
+		kt_zero = kt.x == 0.0 && kt.y == 0.0 && kt.z == 0.0;
+	} else {
+		const rt_material& m = S.mats[ob.material];
+		trans = m.trans != 0;
+		kt_zero = m.tex[RT_KT] < 0 && kt_is_zero(m.k[RT_KT]);
+	}
+	anyhit_classify(Y, t, inside, trans, kt_zero);
+}
 
 // emit one all-hits record of an analytic primitive (object space -> world)
 struct ListEmit {
@@ -208,6 +320,7 @@ struct Walk {
 	const DTri* tris;    // the current mesh's triangles
 	TravClosest* C;
 	SBuf* B;
+	AnyHit* Y;
 	int mode;
 	bool prune;
 };
@@ -221,7 +334,7 @@ RT_COLD int walk_begin(const DScene& S, Walk& W, RayF& F, float& limf)
 	make_inv(W.I, F, W.o, W.d, W.prune ? S.scene_slack : 0.0, S.scene_slack * 1e9);
 	W.nodes = S.snodes2;
 	W.tris = S.tris;
-	W.lim = W.mode == TRAV_CLOSEST ? RT_T_INF : W.B->cut;
+	W.lim = W.mode == TRAV_CLOSEST ? RT_T_INF : (W.mode == TRAV_SHADOW ? W.B->cut : W.Y->limit);
 	limf = f_up(W.lim);
 	W.V.len = 1.0;
 	W.V.obj = -1;
@@ -282,6 +395,10 @@ template <int FIXED_MODE> RT_COLD void walk_leaf_tris(const DScene& S, Walk& W, 
 				V.best_pos = pos;
 				if (t < W.lim) W.lim = t;
 			}
+		} else if (mode == TRAV_ANYHIT) {
+			face_anyhit(S, W.V.obj, pos, W.V.len, W.o, W.d, W.dw, *W.Y);
+			if (W.Y->fl & SH_DEAD) { sp = 0; break; } // settled: leave through the pop section's one way out
+			if (W.Y->fl & SH_NEWLIM) { W.Y->fl &= ~SH_NEWLIM; W.lim = lim_to_local(W.Y->prune(), W.V.len); }
 		} else {
 			emit_face(S, W.V.obj, (unsigned)W.V.rank, pos, W.V.len, W.o, W.d, W.dw, *W.B);
 			if (W.B->dead) { sp = 0; break; } // any-hit exit (rt_shadow.cuh): leave through the pop section's one way out
@@ -362,6 +479,10 @@ template <int FIXED_MODE> RT_COLD int walk_leaf_items(const DScene& S, Walk& W, 
 		if (mode == TRAV_CLOSEST) {
 			prim_closest(ob, L, rank, obj, *W.C);
 			if (W.C->have) W.lim = W.C->best_t;
+		} else if (mode == TRAV_ANYHIT) {
+			prim_anyhit(S, ob, L, W.dw, *W.Y);
+			if (W.Y->fl & SH_DEAD) { sp = 0; break; }
+			if (W.Y->fl & SH_NEWLIM) { W.Y->fl &= ~SH_NEWLIM; W.lim = W.Y->prune(); }
 		} else {
 			prim_list(S, ob, L, W.dw, rank, *W.B);
 			if (W.B->dead) { sp = 0; break; } // any-hit exit, as above
@@ -396,7 +517,7 @@ template <int FIXED_MODE> RT_COLD void walk_mesh_exit(const DScene& S, Walk& W, 
 	W.nodes = S.snodes2;
 	nodesf = S.snodes2f;
 	level = 0;
-	W.lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : W.B->cut;
+	W.lim = mode == TRAV_CLOSEST ? (C.have ? C.best_t : RT_T_INF) : (mode == TRAV_SHADOW ? W.B->cut : W.Y->prune());
 	limf = f_up(W.lim);
 }
 
@@ -408,16 +529,17 @@ template <int FIXED_MODE> RT_COLD void walk_mesh_exit(const DScene& S, Walk& W, 
 // All ways out of the loop are in the pop section: a second exit inside the node or leaf loops costs
 // the warp its reconvergence points (profiles/r1_variants.txt: 3x slower).
 template <bool PRUNE, int FIXED_MODE = -1>
-RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B, int budget = 0, const DNode2f* top = nullptr)
+RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_arg, TravClosest& C, SBuf& B, int budget = 0, const DNode2f* top = nullptr, AnyHit* Y = nullptr)
 {
 	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : mode_arg;
 	RT_WORK_SCOPE(mode);
-	const bool prune = PRUNE || mode == TRAV_SHADOW;
+	const bool prune = PRUNE || mode != TRAV_CLOSEST;
 	Walk W;
 	W.ow = ow;
 	W.dw = dw;
 	W.C = &C;
 	W.B = &B;
+	W.Y = Y;
 	W.mode = mode;
 	W.prune = prune;
 	StackEnt stk[RT_STACK];

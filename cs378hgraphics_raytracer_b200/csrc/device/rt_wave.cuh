@@ -71,6 +71,7 @@ struct WaveCounters {
 	unsigned long long heavy_cursor; // next heavy ray to be taken by a warp
 	unsigned long long n_retry;      // rays that exhausted the FIRST budget (k_wave_closest); k_wave_closest_retry walks them
 	                                 // again with a larger one and only its leftovers (n_heavy) go to the cooperative kernel
+	unsigned long long n_complex[2]; // per round parity: shadow rays the any-hit kernel could not decide (k_wave_shadow_list walks them)
 	unsigned long long n_shadow[2];  // per round parity: the shadow rays of round r are still being
 	                                 // walked (second stream) while round r+1 fills the other queue
 };
@@ -463,6 +464,84 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 		if (shadow_walk(st, B, Lt, rd, A.prm)) break;
 	}
 	accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
+}
+
+// ---- stage 3, two-kernel form: decide by classification, walk completely only what needs it ---------------------------
+// k_wave_shadow carries everything srsAttenuation can need - the sorted window of hits, kt evaluation (textures, per-vertex
+// blends), the attenuation walk with pow - and ncu showed instruction fetch as its largest stall class (7.1 stalled warps per
+// issue against 0.5 in k_wave_closest: a 120 KB image).  But a scene's shadow rays are mostly either blocked by an opaque
+// surface in the near half of the segment (result exactly 0) or meet nothing (exactly 1): 95 % of C5's.  So:
+//   k_wave_shadow_any   every ray: the walk in TRAV_ANYHIT mode (rt_traverse.cuh) - hits are classified where they are found,
+//                       an entered opaque surface at t <= 0.49 D stops the walk at once; 0 -> nothing to add, no hit -> the
+//                       Phong term is added; anything else (a transmissive surface, a far-half hit, an origin inside an
+//                       object, an area or spot light) -> the ray is listed.
+//   k_wave_shadow_list  the listed rays: the complete walk, unchanged (persistent grid over the list).
+// Both shortcuts are exits the complete walk takes itself, so the frame is the same bit for bit.
+#ifndef RT_ANY_MINB
+#define RT_ANY_MINB 16
+#endif
+__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_ANY_MINB) k_wave_shadow_any(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, WaveCounters* cnt,
+                                                                                 const unsigned* __restrict__ perm, int sparse, int* complex_list)
+{
+	RT_STAGE_TOP(S, top);
+	const unsigned lane = threadIdx.x & 31;
+	const long long t0 = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x;
+	const long long k0 = t0 >> sparse;
+	long long n = (long long)cnt->n_shadow[parity];
+	if (n > SQ.cap) n = SQ.cap;
+	const bool valid = (t0 & ((1ll << sparse) - 1)) == 0 && k0 < n; // (no early return: the listing below is a warp operation)
+	bool complex_ray = false;
+	long long k = 0;
+	if (valid) {
+		k = perm ? (long long)perm[k0] : k0;
+		const d3 ro = SQ.load_v(0, k), rd = SQ.load_v(3, k);
+		const rt_light& Lt = S.lights[SQ.i[SQ.cap + k]];
+		AnyHit Y;
+		Y.limit = RT_T_INF;
+		Y.sure_t = RT_T_INF;
+		Y.fl = 0;
+		Y.t_x = RT_T_INF;
+		Y.t_o = RT_T_INF;
+		if (Lt.type == RT_LIGHT_POINT) { // shadow_begin's numbers
+			const double D = length(ld3(Lt.position) - ro);
+			Y.limit = D * (1.0 + 1e-9) + 1e-9;
+			Y.sure_t = 0.49 * D;
+		} else if (Lt.type != RT_LIGHT_DIRECTIONAL) Y.fl = SH_OTHER; // area and spot lights: no any-hit exit, the complete walk
+		if (!Y.fl) {
+			TravClosest unused_c;
+			SBuf* unused_b = nullptr;
+			traverse<true, TRAV_ANYHIT>(S, ro, rd, TRAV_ANYHIT, unused_c, *unused_b, 0, top, &Y);
+		}
+		if (!(Y.fl & SH_DEAD) && !Y.settled_by_exit()) {
+			if (Y.fl & SH_OTHER) complex_ray = true;
+			else accumulate(A.accum, SQ.i[k], SQ.load_v(6, k)); // nothing before the light: attenuation exactly (1,1,1)
+		}
+	}
+	const long long s = wave_reserve(complex_ray, (1u << lane) - 1u, &cnt->n_complex[parity]);
+	if (s >= 0) complex_list[s] = (int)k;
+}
+
+__global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shadow_list(const __grid_constant__ DScene S, const __grid_constant__ PoolArgs A, const RayQueue SQ, int parity, const WaveCounters* cnt,
+                                                                                     const int* __restrict__ complex_list)
+{
+	RT_STAGE_TOP(S, top);
+	const long long n = (long long)cnt->n_complex[parity];
+	for (long long j = (long long)blockIdx.x * RT_TRACE_THREADS + threadIdx.x; j < n; j += (long long)gridDim.x * RT_TRACE_THREADS) {
+		const long long k = complex_list[j];
+		const d3 ro = SQ.load_v(0, k), rd = SQ.load_v(3, k);
+		const rt_light& Lt = S.lights[SQ.i[SQ.cap + k]];
+		ShadowState st;
+		SBuf B;
+		TravClosest unused;
+		unused.have = false;
+		shadow_begin(st, B, Lt, ro);
+		for (;;) {
+			shadow_pass_reset(st, B);
+			traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B, 0, top);
+			if (shadow_walk(st, B, Lt, rd, A.prm)) break;
+		}
+		accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
+	}
 }
 
 // spill / take back: n entries of a 12-double queue, src[src0 ...] -> dst[dst0 ...]

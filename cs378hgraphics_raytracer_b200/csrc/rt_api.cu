@@ -47,6 +47,13 @@ struct rt_ctx {
 	                                              // tail of round r-1's shadow kernel: a launch lasts as long as its slowest ray
 	cudaEvent_t ev_shade[2] = {nullptr, nullptr}, ev_shadow[2] = {nullptr, nullptr};
 	bool overlap = true;                   // RT_B200_OVERLAP=0: everything on one stream
+	// any-hit shadow stage: fraction of round r's shadow rays it left to the complete walk, from the last frame of this scene
+	// (a property of the scene and the settings, round by round: primary hits see mostly opaque blockers, deep bounces sit
+	// inside glass); a round whose fraction is above the break-even is walked once, completely
+	double undecided[32] = {0};
+	long long any_n[2] = {0, 0};           // rays of the any-hit launch in flight per round parity (0: that launch was one-kernel)
+	int any_round[2] = {0, 0};             // ... and the round it belongs to
+	bool shadow_two = true;                // RT_B200_ANYHIT=0: one shadow kernel (k_wave_shadow) instead of any-hit classification + complete walk of the rest
 	bool sparse_small = true;              // RT_B200_SPARSE=0: small rounds are launched densely (32 rays per warp) like large ones
 	bool sort_closest = true;              // RT_B200_SORTC=0: reflection / refraction rays are walked in queue order instead of (octant, origin cell) order
 	bool sort_shadow = true;               // RT_B200_SORT=0: shadow rays are walked in queue order instead of (light, origin cell) order
@@ -66,7 +73,7 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_STOP, B_COUNT };
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_CX_A, B_CX_B, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_STOP, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -119,6 +126,7 @@ rt_status check_params(rt_ctx* ctx, const rt_params* p)
 	return RT_OK;
 }
 
+#define RT_UNDECIDED_MAX 0.13
 #define RT_SORT_MIN (1ll << 20) // rounds with fewer possible shadow rays are walked in queue order (a sort is ~20 us of launches)
 // log2 of the lanes given to one ray of a walk launch over n rays: as many as keep the launch within the GPU's resident threads
 static inline int sparse_shift(const rt_ctx* ctx, long long n)
@@ -164,6 +172,31 @@ cudaEvent_t next_event(rt_ctx* ctx)
 		if (ctx->profile) { cudaEventRecord(b_, strm); ctx->spans.push_back({id, a_, b_}); } \
 	} while (0)
 #define STAGE(id, ...) STAGE_ON(ctx->stream, id, __VA_ARGS__)
+
+// The shadow stage of one round over (at most) n rays of queue SQ, on stream s: any-hit classification of every ray, then the
+// complete walk of the rays it could not decide - or, RT_B200_ANYHIT=0, the complete walk for all of them.
+rt_status launch_shadow(rt_ctx* ctx, const PoolArgs& A, const RayQueue& SQ, int par, WaveCounters* cnt, long long n, const unsigned* perm, int ssh, cudaStream_t s, int round_index)
+{
+	// the two-kernel form pays when few rays need the second kernel (break-even measured at about 13 %)
+	const int ri = round_index < 31 ? round_index : 31;
+	if (!ctx->shadow_two || ctx->undecided[ri] > RT_UNDECIDED_MAX) {
+		ctx->any_n[par] = 0;
+		STAGE_ON(s, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(n << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, s>>>(ctx->S, A, SQ, par, cnt, perm, ssh));
+		return RT_OK;
+	}
+	const int bx = par ? B_CX_B : B_CX_A;
+	rt_status st;
+	if ((st = ensure(ctx, bx, (size_t)SQ.cap * sizeof(int))) != RT_OK) return st;
+	int* list = (int*)ctx->buf[bx];
+	ctx->any_n[par] = n;
+	ctx->any_round[par] = ri;
+	CK(cudaMemsetAsync(&cnt->n_complex[par], 0, sizeof(unsigned long long), s));
+	STAGE_ON(s, RT_STAGE_SHADOW, k_wave_shadow_any<<<blocks_for(n << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, s>>>(ctx->S, A, SQ, par, cnt, perm, ssh, list));
+	long long grid = (long long)ctx->sm_count * RT_SHADOW_MINB;
+	if (grid > (long long)blocks_for(n, RT_TRACE_THREADS)) grid = blocks_for(n, RT_TRACE_THREADS);
+	STAGE_ON(s, RT_STAGE_SHADOW, k_wave_shadow_list<<<(unsigned)(grid > 0 ? grid : 1), RT_TRACE_THREADS, 0, s>>>(ctx->S, A, SQ, par, cnt, list));
+	return RT_OK;
+}
 
 // The trace loop over n_slots primary-ray slots as a streaming wavefront (device/rt_wave.cuh).
 rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
@@ -274,9 +307,11 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		// shade stage writes it, so the closest-hit walks above did not have to wait
 		if (shadow_pending[par] && overlap) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_shadow[par], 0));
 		shadow_pending[par] = false;
+		const long long prev_any_n = ctx->any_n[par]; // this parity's previous any-hit launch (two rounds ago) has finished by now
+		const int prev_any_round = ctx->any_round[par];
 		CK(cudaMemsetAsync(&cnt->n_shadow[par], 0, sizeof(unsigned long long), ctx->stream));
 		STAGE(RT_STAGE_SHADE, k_wave_shade<<<blocks_for(m, RT_WAVE_THREADS), RT_WAVE_THREADS, 0, ctx->stream>>>(ctx->S, A, cur, base, m, H, nxt, sq[par], par, cnt));
-		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry, shadow rays [2]
+		CK(cudaMemcpyAsync(ctx->pinned, &cnt->n_children, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream)); // children, heavy, cursor, retry, complex [2], shadow rays [2]
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		// Large rounds: the shadow rays are walked in (light, origin cell) order.  The radix sort needs the number of rays on
 		// the host, which arrives with the counters the host waits for anyway - so the wait moves in front of the launch.
@@ -285,7 +320,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		if (sorted) {
 			CK(cudaEventSynchronize(ctx->ev_round));
 			synced = true;
-			long long ns = (long long)ctx->pinned[4 + par];
+			long long ns = (long long)ctx->pinned[6 + par];
 			if (ns > sq[par].cap) ns = sq[par].cap;
 			cudaStream_t sstream = overlap ? ctx->stream2[par] : ctx->stream;
 			if (overlap) {
@@ -306,7 +341,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 				STAGE_ON(sstream, RT_STAGE_OTHER, k_shadow_keys<<<blocks_for(ns, 256), 256, 0, sstream>>>(ctx->S, sq[par], ns, keys, idx));
 				STAGE_ON(sstream, RT_STAGE_OTHER, CK(cub::DeviceRadixSort::SortPairs(ctx->buf[bt], tmp_bytes, keys, keys + sq[par].cap, idx, idx + sq[par].cap, (int)ns, 0, 32, sstream)));
 				const int ssh = sparse_shift(ctx, ns);
-				STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for(ns << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, idx + sq[par].cap, ssh));
+				if ((st = launch_shadow(ctx, A, sq[par], par, cnt, ns, idx + sq[par].cap, ssh, sstream, (int)round)) != RT_OK) return st;
 			}
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		} else if (L > 0) {
@@ -317,13 +352,14 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 			}
 			// grid sized for the most shadow rays this round can have made; blocks past the count leave at once
 			const int ssh = sparse_shift(ctx, m * L);
-			STAGE_ON(sstream, RT_STAGE_SHADOW, k_wave_shadow<<<blocks_for((m * L) << ssh, RT_TRACE_THREADS), RT_TRACE_THREADS, 0, sstream>>>(ctx->S, A, sq[par], par, cnt, nullptr, ssh));
+			if ((st = launch_shadow(ctx, A, sq[par], par, cnt, m * L, nullptr, ssh, sstream, (int)round)) != RT_OK) return st;
 			if (overlap) { CK(cudaEventRecord(ctx->ev_shadow[par], sstream)); shadow_pending[par] = true; }
 		}
 		CK(cudaGetLastError());
 		if (!synced) CK(cudaEventSynchronize(ctx->ev_round)); // the host plans the next round while the shadow rays run
 		cur_n = (long long)ctx->pinned[0];
 		if (cur_n > nxt.cap) cur_n = nxt.cap; // overflow was flagged by the kernel
+		if (prev_any_n >= 4096) ctx->undecided[prev_any_round] = (double)ctx->pinned[4 + par] / (double)prev_any_n; // n_complex of that launch
 		// the node budget follows the scene: if more than ~1.5 % of a round's rays ran out of it, the
 		// ordinary walk of this scene is simply longer (deep scene-level trees) - double it.  Either
 		// path gives the same hit, so this only moves work between the two kernels.
@@ -422,6 +458,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SPARSE")) ctx->sparse_small = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_ANYHIT")) ctx->shadow_two = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs
 	int per_sm = 0;
@@ -639,6 +676,8 @@ static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes,
 	if (hflags[0]) { ctx->error = "invalid arena: index out of range (device check " + std::to_string(hflags[0]) + ")"; return RT_ERR_ARG; }
 	if ((hflags[1] | hflags[2]) & 0x80000000u || hflags[1] + hflags[2] > RT_STACK - 4) { ctx->error = "trees too deep for the traversal stack"; return RT_ERR_UNSUPPORTED; }
 	if (ctx->budget_auto) ctx->walk_budget = 96;
+	for (int k = 0; k < 32; k++) ctx->undecided[k] = 0.0;
+	ctx->any_n[0] = ctx->any_n[1] = 0;
 	ctx->n_area_lights = n_area;
 	ctx->has_scene = true;
 	return RT_OK;

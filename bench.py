@@ -417,7 +417,7 @@ def measure(S, key, wl, steps, warmup, cpu_seconds, cpu_full_frame):
     out["stages"] = {names[k]: {"ms_per_step": stage_ms[k] / steps, "launches_per_step": stage_n[k] / steps} for k in range(6) if stage_n[k] > 0}
     if cm and stage_ms.sum() > 0:
         closest_ms, shadow_ms = stage_ms[1] + stage_ms[2], stage_ms[4]
-        kind, kernel, k_ms, k_n = ("shadow", "k_wave_shadow", shadow_ms, stage_n[4]) if shadow_ms >= closest_ms else \
+        kind, kernel, k_ms, k_n = ("shadow", "k_wave_shadow_any (+ k_wave_shadow_list)", shadow_ms, stage_n[4]) if shadow_ms >= closest_ms else \
                                   ("closest", "k_wave_closest (+ k_wave_closest_heavy)", closest_ms, stage_n[1])
         ck = cm["kinds"][kind]
         n_rays = kind_rays[0 if kind == "closest" else 1]

@@ -8,7 +8,7 @@ mkdir -p "$OUT"
 cuobjdump -sass "$LIB" | awk -v out="$OUT" '
 /Function :/ {
 	name = $3; keep = 0; file = ""
-	if (name ~ /k_wave_gen|k_wave_closestE|k_wave_closest_retry|k_wave_closest_heavy|k_wave_shade|k_wave_shadow|k_resolve_grid|k_adapt_resolve/) {
+	if (name ~ /k_wave_gen|k_wave_closestE|k_wave_closest_retry|k_wave_closest_heavy|k_wave_shade|k_wave_shadowE|k_wave_shadow_any|k_wave_shadow_list|k_shadow_keys|k_closest_keys|k_resolve_grid|k_adapt_resolve|k_adapt_samples|k_pack_tiles|k_unpack_tiles|k_hits_static/) {
 		short = name; sub(/^_ZN3rtd[0-9]+/, "", short); sub(/E.*/, "", short)
 		file = out "/" short ".sass"; keep = 1
 		print "// " name > file

@@ -31,6 +31,7 @@ struct PoolArgs {
 	int spp_side;       // supersample grid side s (1 = none)
 	int lenses;         // primary rays per sample (1, or divs+1 with depth of field)
 	int part, n_parts;  // this context renders tiles t with t % n_parts == part
+	long long tile0;    // first local tile of this launch (a frame with more samples than one launch takes is rendered in chunks of whole tiles)
 	int tiles_x, tiles_y;
 	int depth;          // traceRay depth of primaries
 	double eye_shift;   // anaglyph second eye
@@ -55,7 +56,7 @@ __device__ __forceinline__ bool grid_sample(const PoolArgs& A, long long sample,
 	const int spp = A.spp_side * A.spp_side;
 	const long long pix = sample / spp;
 	const int sub = (int)(sample % spp);
-	const long long ltile = pix / RT_TILE_PIX;
+	const long long ltile = pix / RT_TILE_PIX + A.tile0;
 	const int p = (int)(pix % RT_TILE_PIX);
 	const long long tile = ltile * A.n_parts + A.part;
 	const int tx = (int)(tile % A.tiles_x), ty = (int)(tile / A.tiles_x);

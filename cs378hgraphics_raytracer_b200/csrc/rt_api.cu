@@ -54,6 +54,7 @@ struct rt_ctx {
 	long long any_n[2] = {0, 0};           // rays of the any-hit launch in flight per round parity (0: that launch was one-kernel)
 	int any_round[2] = {0, 0};             // ... and the round it belongs to
 	bool shadow_two = true;                // RT_B200_ANYHIT=0: one shadow kernel (k_wave_shadow) instead of any-hit classification + complete walk of the rest
+	long long chunk_samples = 1ll << 28;   // camera samples per launch of the grid path (RT_B200_CHUNK; a frame above it is rendered in chunks of tiles)
 	bool sparse_small = true;              // RT_B200_SPARSE=0: small rounds are launched densely (32 rays per warp) like large ones
 	bool sort_closest = true;              // RT_B200_SORTC=0: reflection / refraction rays are walked in queue order instead of (octant, origin cell) order
 	bool sort_shadow = true;               // RT_B200_SORT=0: shadow rays are walked in queue order instead of (light, origin cell) order
@@ -458,6 +459,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SPARSE")) ctx->sparse_small = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_CHUNK")) { const long long v = atoll(e); if (v >= 1024 && v <= (1ll << 30)) ctx->chunk_samples = v; }
 	if (const char* e = getenv("RT_B200_ANYHIT")) ctx->shadow_two = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }
 	// persistent grid: resident CTAs per SM x number of SMs
@@ -751,25 +753,32 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 	if (!adaptive) {
 		A.src = SRC_GRID;
 		A.spp_side = (p->aa_mode == RT_AA_SUPERSAMPLE || p->aa_mode == RT_AA_JITTERED) ? p->aa_samples : 1;
-		const long long n_samples = n_pix * A.spp_side * A.spp_side;
-		if (n_samples > 0x7fffffffll) { ctx->error = "too many samples for one launch"; return RT_ERR_UNSUPPORTED; }
-		A.n_slots = n_samples * A.lenses;
-		if ((st = ensure(ctx, B_ACCUM, (size_t)n_samples * 24)) != RT_OK) return st;
-		A.accum = (double*)ctx->buf[B_ACCUM];
-		CK(cudaMemsetAsync(A.accum, 0, (size_t)n_samples * 24, ctx->stream));
-		if ((st = launch_wave(ctx, A)) != RT_OK) return st;
-		double* accum2 = nullptr;
-		if (p->anaglyph) { // second eye, shifted by ANAGLYPH_DELTA (RayTracer.cpp:23,92-99)
-			if ((st = ensure(ctx, B_ACCUM2, (size_t)n_samples * 24)) != RT_OK) return st;
-			accum2 = (double*)ctx->buf[B_ACCUM2];
-			CK(cudaMemsetAsync(accum2, 0, (size_t)n_samples * 24, ctx->stream));
-			PoolArgs A2 = A;
-			A2.accum = accum2;
-			A2.eye_shift = 0.25;
-			if ((st = launch_wave(ctx, A2)) != RT_OK) return st;
-		}
-		if (n_pix > 0) {
-			k_resolve_grid<<<blocks_for(n_pix, 256), 256, 0, ctx->stream>>>(A, accum2, n_pix, fb);
+		// The frame is rendered in chunks of whole tiles: a sample index must fit 31 bits (the queues carry it in an int) and the
+		// accumulators (24 B per sample) must fit the device - an 8K frame at 8x8 supersampling has 2.1 G samples.  The five
+		// configurations are one chunk each.
+		const long long spt = (long long)RT_TILE_PIX * A.spp_side * A.spp_side; // samples per tile
+		long long chunk_tiles = ctx->chunk_samples / spt;
+		if (chunk_tiles < 1) chunk_tiles = 1;
+		for (long long t0 = 0; t0 < local_tiles; t0 += chunk_tiles) {
+			const long long tiles_c = local_tiles - t0 < chunk_tiles ? local_tiles - t0 : chunk_tiles;
+			const long long n_pix_c = tiles_c * RT_TILE_PIX, n_samples = tiles_c * spt;
+			A.tile0 = t0;
+			A.n_slots = n_samples * A.lenses;
+			if ((st = ensure(ctx, B_ACCUM, (size_t)n_samples * 24)) != RT_OK) return st;
+			A.accum = (double*)ctx->buf[B_ACCUM];
+			CK(cudaMemsetAsync(A.accum, 0, (size_t)n_samples * 24, ctx->stream));
+			if ((st = launch_wave(ctx, A)) != RT_OK) return st;
+			double* accum2 = nullptr;
+			if (p->anaglyph) { // second eye, shifted by ANAGLYPH_DELTA (RayTracer.cpp:23,92-99)
+				if ((st = ensure(ctx, B_ACCUM2, (size_t)n_samples * 24)) != RT_OK) return st;
+				accum2 = (double*)ctx->buf[B_ACCUM2];
+				CK(cudaMemsetAsync(accum2, 0, (size_t)n_samples * 24, ctx->stream));
+				PoolArgs A2 = A;
+				A2.accum = accum2;
+				A2.eye_shift = 0.25;
+				if ((st = launch_wave(ctx, A2)) != RT_OK) return st;
+			}
+			k_resolve_grid<<<blocks_for(n_pix_c, 256), 256, 0, ctx->stream>>>(A, accum2, n_pix_c, fb);
 			ctx->launches++;
 			CK(cudaGetLastError());
 		}

@@ -588,3 +588,31 @@ def test_adaptive_termination_all_scenes(rtlib, oracle_mod, ctx, scene_path, sce
     # and the switch really prunes: fewer secondary rays than without it (where the scene has any)
     _, full_st = ctx.render(rtlib.Params.default(depth=5), w, h)
     assert dev_st.reflection_rays + dev_st.refraction_rays <= full_st.reflection_rays + full_st.refraction_rays
+
+
+def test_chunked_frame_is_the_same_frame(rtlib, ctx, scene_dir, monkeypatch):
+    """A frame with more camera samples than one launch takes (2^28 by default; an 8K frame at 8x8 supersampling has 2.1 G) is
+    rendered in chunks of whole tiles.  Forced down to 4096 samples per launch, a small frame goes through dozens of chunks:
+    same pixels, same ray counts - plain, supersampled on a 3-way tile partition, and with the anaglyph second eye."""
+    arena = rtlib.load_ray_file(str(scene_dir / "prims_mixed.ray"))
+    ctx.upload(arena)
+    monkeypatch.setenv("RT_B200_CHUNK", "4096")
+    c = rtlib.Context(0)
+    try:
+        c.upload(arena)
+        w, h = 200, 150
+        for kw, parts in ((dict(), 1), (dict(aa_mode=1, aa_samples=2), 3), (dict(anaglyph=1), 1)):
+            p = rtlib.Params.default(depth=4, **kw)
+            want = np.zeros((h, w, 3), np.uint8)
+            got = np.zeros((h, w, 3), np.uint8)
+            n_want = n_got = 0
+            for part in range(parts):
+                _, st = ctx.render(p, w, h, part, parts, out=want)
+                n_want += st.rays
+                _, st = c.render(p, w, h, part, parts, out=got)
+                n_got += st.rays
+                assert st.rounds > 20  # many launches of the wavefront, one per chunk
+            _assert_same_frame(got, want)
+            assert n_got == n_want
+    finally:
+        c.close()

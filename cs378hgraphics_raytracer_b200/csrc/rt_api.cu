@@ -20,6 +20,7 @@ extern "C" rt_status rt_arena_validate_tables(const void* arena, size_t bytes); 
 
 using namespace rtd;
 
+#define RT_SORT_MIN (1ll << 20) // rounds with fewer possible shadow rays are walked in queue order (a sort is ~20 us of launches)
 struct rt_ctx {
 	int device = 0;
 	cudaStream_t stream = nullptr;
@@ -54,6 +55,7 @@ struct rt_ctx {
 	long long any_n[2] = {0, 0};           // rays of the any-hit launch in flight per round parity (0: that launch was one-kernel)
 	int any_round[2] = {0, 0};             // ... and the round it belongs to
 	bool shadow_two = true;                // RT_B200_ANYHIT=0: one shadow kernel (k_wave_shadow) instead of any-hit classification + complete walk of the rest
+	long long sort_min = RT_SORT_MIN;      // rounds with fewer rays are walked in queue order (RT_B200_SORTMIN)
 	long long chunk_samples = 1ll << 28;   // camera samples per launch of the grid path (RT_B200_CHUNK; a frame above it is rendered in chunks of tiles)
 	bool sparse_small = true;              // RT_B200_SPARSE=0: small rounds are launched densely (32 rays per warp) like large ones
 	bool sort_closest = true;              // RT_B200_SORTC=0: reflection / refraction rays are walked in queue order instead of (octant, origin cell) order
@@ -128,7 +130,6 @@ rt_status check_params(rt_ctx* ctx, const rt_params* p)
 }
 
 #define RT_UNDECIDED_MAX 0.13
-#define RT_SORT_MIN (1ll << 20) // rounds with fewer possible shadow rays are walked in queue order (a sort is ~20 us of launches)
 // log2 of the lanes given to one ray of a walk launch over n rays: as many as keep the launch within the GPU's resident threads
 static inline int sparse_shift(const rt_ctx* ctx, long long n)
 {
@@ -282,7 +283,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		// a forced budget (RT_B200_BUDGET, the tests) sends its leftovers straight to the cooperative kernel
 		const bool second = ctx->budget_auto && ctx->walk_budget > 0;
 		const unsigned* cperm = nullptr;
-		if (ctx->sort_closest && n_kids >= RT_SORT_MIN) {
+		if (ctx->sort_closest && n_kids >= ctx->sort_min) {
 			if ((st = ensure(ctx, B_CK, (size_t)W * 2 * sizeof(unsigned))) != RT_OK) return st;
 			if ((st = ensure(ctx, B_CI, (size_t)W * 2 * sizeof(unsigned))) != RT_OK) return st;
 			unsigned* keys = (unsigned*)ctx->buf[B_CK];
@@ -316,7 +317,7 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 		CK(cudaEventRecord(ctx->ev_round, ctx->stream));
 		// Large rounds: the shadow rays are walked in (light, origin cell) order.  The radix sort needs the number of rays on
 		// the host, which arrives with the counters the host waits for anyway - so the wait moves in front of the launch.
-		const bool sorted = L > 0 && ctx->sort_shadow && m * L >= RT_SORT_MIN;
+		const bool sorted = L > 0 && ctx->sort_shadow && m * L >= ctx->sort_min;
 		bool synced = false;
 		if (sorted) {
 			CK(cudaEventSynchronize(ctx->ev_round));
@@ -459,6 +460,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SPARSE")) ctx->sparse_small = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_SORTMIN")) { const long long v = atoll(e); if (v >= 1024) ctx->sort_min = v; }
 	if (const char* e = getenv("RT_B200_CHUNK")) { const long long v = atoll(e); if (v >= 1024 && v <= (1ll << 30)) ctx->chunk_samples = v; }
 	if (const char* e = getenv("RT_B200_ANYHIT")) ctx->shadow_two = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_BUDGET")) { const int v = atoi(e); if (v >= 0) { ctx->walk_budget = v; ctx->budget_auto = false; } }

@@ -15,6 +15,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "rt_shade.cuh"
+#include "rt_accum.cuh"
 
 namespace rtd {
 
@@ -39,7 +40,8 @@ struct PoolArgs {
 	const double* xs;   // SRC_XY: sample window coordinates
 	const double* ys;
 	const rt_ray* rays; // SRC_RAYS
-	double* accum;      // 3 doubles per sample
+	long long* accum;   // RT_ACC_STRIDE limbs per sample (rt_accum.cuh)
+	double* base;       // 3 doubles per sample: the camera ray's own term, stored instead of added (nullptr with depth of field: several camera rays per sample)
 	unsigned long long* cursor;
 	unsigned long long* stats; // camera, reflection, refraction, shadow, overflow flag
 	double* pool_d;     // per warp: RT_POOL_DOUBLES x cap doubles
@@ -98,9 +100,9 @@ __global__ void __launch_bounds__(128) k_hits(const DScene S, const rt_ray* rays
 }
 
 // RayTracer::trace's tail for one sample (RayTracer.cpp:74-78): mean over the lens rays, clamp
-__device__ __forceinline__ d3 sample_value(const double* accum, long long sample, const rt_params& prm)
+__device__ __forceinline__ d3 sample_value(const long long* accum, const double* base, long long sample, const rt_params& prm)
 {
-	d3 c = mk3(accum[3 * sample], accum[3 * sample + 1], accum[3 * sample + 2]);
+	d3 c = acc_read3(accum, base, sample);
 	if (prm.dof_on) c = c * (1.0 / (prm.dof_divs + 1.0));
 	return gclamp(c, 0.0, 1.0);
 }
@@ -116,7 +118,7 @@ __device__ __forceinline__ void store_pixel(uint8_t* fb, int w, int i, int j, d3
 
 // No-AA and supersampled resolve (RayTracer.cpp:288-298, 310): one thread per local pixel.
 // accum2 (optional) holds the anaglyph second-eye samples whose red channel replaces the first's.
-__global__ void __launch_bounds__(256) k_resolve_grid(const PoolArgs A, const double* accum2, long long n_pix, uint8_t* fb)
+__global__ void __launch_bounds__(256) k_resolve_grid(const PoolArgs A, const long long* accum2, const double* base2, long long n_pix, uint8_t* fb)
 {
 	const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (pix >= n_pix) return;
@@ -126,8 +128,8 @@ __global__ void __launch_bounds__(256) k_resolve_grid(const PoolArgs A, const do
 	if (!grid_sample(A, pix * spp, pi, pj, x, y)) return;
 	d3 col = mk3(0.0, 0.0, 0.0);
 	for (int s = 0; s < spp; s++) {
-		d3 c = sample_value(A.accum, pix * spp + s, A.prm);
-		if (accum2) c.x = sample_value(accum2, pix * spp + s, A.prm).x;
+		d3 c = sample_value(A.accum, A.base, pix * spp + s, A.prm);
+		if (accum2) c.x = sample_value(accum2, base2, pix * spp + s, A.prm).x;
 		col = col + c;
 	}
 	if (spp > 1) {
@@ -186,19 +188,19 @@ __global__ void __launch_bounds__(256) k_adapt_samples(const Region* regions, lo
 // mean / deviation test of each region; either adds its mean (scaled by 4^-level) to the pixel or
 // emits its four quadrants for the next level.
 
-__global__ void __launch_bounds__(256) k_adapt_resolve(const Region* regions, long long n_regions, int N, const double* accum, rt_params prm,
-                                                      double* pix_accum, Region* next, unsigned long long* next_count, unsigned long long next_cap)
+__global__ void __launch_bounds__(256) k_adapt_resolve(const Region* regions, long long n_regions, int N, const long long* accum, const double* base, rt_params prm,
+                                                      long long* pix_accum, Region* next, unsigned long long* next_count, unsigned long long next_cap)
 {
 	const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= n_regions) return;
 	const Region r = regions[t];
 	if (!region_valid(r)) return; // val left at its zero initialisation
 	d3 mu = mk3(0.0, 0.0, 0.0);
-	for (int k = 0; k < N; k++) mu = mu + sample_value(accum, t * N + k, prm);
+	for (int k = 0; k < N; k++) mu = mu + sample_value(accum, base, t * N + k, prm);
 	mu = mu * (1.0 / N);
 	d3 sd = mk3(0.0, 0.0, 0.0);
 	for (int k = 0; k < N; k++) {
-		const d3 c = sample_value(accum, t * N + k, prm);
+		const d3 c = sample_value(accum, base, t * N + k, prm);
 		const d3 a = mk3(fabs(c.x - mu.x), fabs(c.y - mu.y), fabs(c.z - mu.z));
 		sd = sd + a * a; // pow(|s - mu|, 2.0) is the correctly rounded square
 	}
@@ -221,19 +223,21 @@ __global__ void __launch_bounds__(256) k_adapt_resolve(const Region* regions, lo
 		return;
 	}
 	mu = mu * scale;
-	atomicAdd(pix_accum + 3ll * r.pix + 0, mu.x);
-	atomicAdd(pix_accum + 3ll * r.pix + 1, mu.y);
-	atomicAdd(pix_accum + 3ll * r.pix + 2, mu.z);
+	// the regions of a pixel finish in any order: integer limbs again
+	long long* pa = pix_accum + (long long)RT_ACC_STRIDE * r.pix;
+	acc_add(pa + 0, mu.x);
+	acc_add(pa + 2, mu.y);
+	acc_add(pa + 4, mu.z);
 }
 
-__global__ void __launch_bounds__(256) k_adapt_store(const PoolArgs A, long long n_pix, const double* pix_accum, uint8_t* fb)
+__global__ void __launch_bounds__(256) k_adapt_store(const PoolArgs A, long long n_pix, const long long* pix_accum, uint8_t* fb)
 {
 	const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (pix >= n_pix) return;
 	int pi, pj;
 	double x, y;
 	if (!grid_sample(A, pix, pi, pj, x, y)) return;
-	store_pixel(fb, A.w, pi, pj, mk3(pix_accum[3 * pix], pix_accum[3 * pix + 1], pix_accum[3 * pix + 2]));
+	store_pixel(fb, A.w, pi, pj, acc_read3(pix_accum, nullptr, pix));
 }
 
 } // namespace rtd
@@ -271,12 +275,23 @@ __global__ void __launch_bounds__(256) k_unpack_tiles(const uint8_t* __restrict_
 
 // RayTracer::tracePixel's return value for explicit samples (clamped mean over lens rays,
 // anaglyph red from the second eye)
-__global__ void __launch_bounds__(256) k_sample_values(const double* accum, const double* accum2, long long n, rt_params prm, double* out)
+__global__ void __launch_bounds__(256) k_sample_values(const long long* accum, const double* base, const long long* accum2, const double* base2, long long n, rt_params prm, double* out)
 {
 	const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (k >= n) return;
-	d3 c = sample_value(accum, k, prm);
-	if (accum2) c.x = sample_value(accum2, k, prm).x;
+	d3 c = sample_value(accum, base, k, prm);
+	if (accum2) c.x = sample_value(accum2, base2, k, prm).x;
+	out[3 * k] = c.x;
+	out[3 * k + 1] = c.y;
+	out[3 * k + 2] = c.z;
+}
+
+// traceRay's own return value for explicit rays (rt_trace_rays): the sums as they are, not clamped
+__global__ void __launch_bounds__(256) k_accum_values(const long long* accum, const double* base, long long n, double* out)
+{
+	const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	const d3 c = acc_read3(accum, base, k);
 	out[3 * k] = c.x;
 	out[3 * k + 1] = c.y;
 	out[3 * k + 2] = c.z;

@@ -56,13 +56,33 @@ __device__ __forceinline__ int pool_reserve(bool pred, unsigned lt_mask, int& co
 	return pred ? slot : -1;
 }
 
-__device__ __forceinline__ void accumulate(double* accum, int sample, const d3& c)
+// one term of a sample's colour (rt_accum.cuh: integer limbs, the same total in any order)
+__device__ __forceinline__ void accumulate(long long* accum, int sample, const d3& c)
 {
-	double* acc = accum + 3ll * sample;
-	if (c.x != 0.0) atomicAdd(acc + 0, c.x);
-	if (c.y != 0.0) atomicAdd(acc + 1, c.y);
-	if (c.z != 0.0) atomicAdd(acc + 2, c.z);
+	long long* acc = accum + (long long)RT_ACC_STRIDE * sample;
+	if (c.x != 0.0) acc_add(acc + 0, c.x);
+	if (c.y != 0.0) acc_add(acc + 2, c.y);
+	if (c.z != 0.0) acc_add(acc + 4, c.z);
 }
+
+// a ray's own term (emission + ambient, or the background): the camera ray's is the only one of its sample, a plain store
+__device__ __forceinline__ void add_term(const PoolArgs& A, int sample, bool camera, const d3& c)
+{
+	if (camera && A.base) {
+		double* b = A.base + 3ll * sample;
+		b[0] = c.x; b[1] = c.y; b[2] = c.z;
+	} else {
+		accumulate(A.accum, sample, c);
+	}
+}
+
+// the same as a real call, for kernels whose register budget is the tighter constraint (RT_ACC_COLD_SHADOW, A/B in profiles/r2_variants.txt)
+__device__ __noinline__ void accumulate_cold(long long* accum, int sample, const d3& c) { accumulate(accum, sample, c); }
+#ifdef RT_ACC_COLD_SHADOW
+#define accumulate_shadow accumulate_cold
+#else
+#define accumulate_shadow accumulate
+#endif
 
 // DEFER = true : shadow rays are pool entries (normal case)
 // DEFER = false: shadow rays traced inline by the shading lane (adaptive termination needs the

@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 		else n_refr = 1;
 		const double t = H.t[k];
 		if (t < 0.0) {
-			accumulate(A.accum, sample, weight * miss_colour(S, A.prm, rd));
+			add_term(A, sample, kind == KIND_CAMERA, weight * miss_colour(S, A.prm, rd));
 		} else {
 			const int2 of = H.of[k];
 			h.obj = of.x;
@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 			finalize_hit(S, ro, rd, h);
 			w = apply_att(weight, Q.load_v(9, q), (meta >> 8) & 15, h.t);
 			eval_material(S, h, me);
-			accumulate(A.accum, sample, w * (me.ke + me.ka * ld3(S.glob.ambient)));
+			add_term(A, sample, kind == KIND_CAMERA, w * (me.ke + me.ka * ld3(S.glob.ambient)));
 			hitP = ro + h.t * rd;
 			lit = true;
 			spawn_children(me, h, ro, rd, w, (meta & 255) - 1, kid, has_refl, has_refr);
@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 		traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B, 0, top);
 		if (shadow_walk(st, B, Lt, rd, A.prm)) break;
 	}
-	accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
+	accumulate_shadow(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
 }
 
 // ---- stage 3, two-kernel form: decide by classification, walk completely only what needs it ---------------------------
@@ -514,7 +514,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_ANY_MINB) k_wave_shadow_a
 		}
 		if (!(Y.fl & SH_DEAD) && !Y.settled_by_exit()) {
 			if (Y.fl & SH_OTHER) complex_ray = true;
-			else accumulate(A.accum, SQ.i[k], SQ.load_v(6, k)); // nothing before the light: attenuation exactly (1,1,1)
+			else accumulate_shadow(A.accum, SQ.i[k], SQ.load_v(6, k)); // nothing before the light: attenuation exactly (1,1,1)
 		}
 	}
 	const long long s = wave_reserve(complex_ray, (1u << lane) - 1u, &cnt->n_complex[parity]);
@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 			traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B, 0, top);
 			if (shadow_walk(st, B, Lt, rd, A.prm)) break;
 		}
-		accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
+		accumulate_shadow(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
 	}
 }
 

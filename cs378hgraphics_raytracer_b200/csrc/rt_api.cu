@@ -76,7 +76,7 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_CX_A, B_CX_B, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_STOP, B_COUNT };
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_CX_A, B_CX_B, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_STOP, B_BASE, B_BASE2, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -432,6 +432,23 @@ rt_status read_stats(rt_ctx* ctx, rt_stats* stats, float ms)
 
 } // namespace
 
+// zeroed sample accumulators for one launch: the limbs (rt_accum.cuh) and, when a sample has exactly one camera ray,
+// the array that ray's own term is stored in
+static rt_status prepare_accum(rt_ctx* ctx, PoolArgs& A, int b_accum, int b_base, long long n_samples)
+{
+	rt_status st;
+	if ((st = ensure(ctx, b_accum, (size_t)n_samples * RT_ACC_BYTES)) != RT_OK) return st;
+	A.accum = (long long*)ctx->buf[b_accum];
+	CK(cudaMemsetAsync(A.accum, 0, (size_t)n_samples * RT_ACC_BYTES, ctx->stream));
+	A.base = nullptr;
+	if (A.lenses == 1) {
+		if ((st = ensure(ctx, b_base, (size_t)n_samples * 24)) != RT_OK) return st;
+		A.base = (double*)ctx->buf[b_base];
+		CK(cudaMemsetAsync(A.base, 0, (size_t)n_samples * 24, ctx->stream));
+	}
+	return RT_OK;
+}
+
 extern "C" {
 
 rt_status rt_create(int device, rt_ctx** out)
@@ -756,7 +773,7 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 		A.src = SRC_GRID;
 		A.spp_side = (p->aa_mode == RT_AA_SUPERSAMPLE || p->aa_mode == RT_AA_JITTERED) ? p->aa_samples : 1;
 		// The frame is rendered in chunks of whole tiles: a sample index must fit 31 bits (the queues carry it in an int) and the
-		// accumulators (24 B per sample) must fit the device - an 8K frame at 8x8 supersampling has 2.1 G samples.  The five
+		// accumulators (48 B per sample) must fit the device - an 8K frame at 8x8 supersampling has 2.1 G samples.  The five
 		// configurations are one chunk each.
 		const long long spt = (long long)RT_TILE_PIX * A.spp_side * A.spp_side; // samples per tile
 		long long chunk_tiles = ctx->chunk_samples / spt;
@@ -766,30 +783,26 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 			const long long n_pix_c = tiles_c * RT_TILE_PIX, n_samples = tiles_c * spt;
 			A.tile0 = t0;
 			A.n_slots = n_samples * A.lenses;
-			if ((st = ensure(ctx, B_ACCUM, (size_t)n_samples * 24)) != RT_OK) return st;
-			A.accum = (double*)ctx->buf[B_ACCUM];
-			CK(cudaMemsetAsync(A.accum, 0, (size_t)n_samples * 24, ctx->stream));
+			if ((st = prepare_accum(ctx, A, B_ACCUM, B_BASE, n_samples)) != RT_OK) return st;
 			if ((st = launch_wave(ctx, A)) != RT_OK) return st;
-			double* accum2 = nullptr;
+			PoolArgs A2 = A;
+			A2.accum = nullptr;
+			A2.base = nullptr;
 			if (p->anaglyph) { // second eye, shifted by ANAGLYPH_DELTA (RayTracer.cpp:23,92-99)
-				if ((st = ensure(ctx, B_ACCUM2, (size_t)n_samples * 24)) != RT_OK) return st;
-				accum2 = (double*)ctx->buf[B_ACCUM2];
-				CK(cudaMemsetAsync(accum2, 0, (size_t)n_samples * 24, ctx->stream));
-				PoolArgs A2 = A;
-				A2.accum = accum2;
+				if ((st = prepare_accum(ctx, A2, B_ACCUM2, B_BASE2, n_samples)) != RT_OK) return st;
 				A2.eye_shift = 0.25;
 				if ((st = launch_wave(ctx, A2)) != RT_OK) return st;
 			}
-			k_resolve_grid<<<blocks_for(n_pix_c, 256), 256, 0, ctx->stream>>>(A, accum2, n_pix_c, fb);
+			k_resolve_grid<<<blocks_for(n_pix_c, 256), 256, 0, ctx->stream>>>(A, A2.accum, A2.base, n_pix_c, fb);
 			ctx->launches++;
 			CK(cudaGetLastError());
 		}
 	} else {
 		A.spp_side = 1;
 		const int N = p->aa_samples * p->aa_samples;
-		if ((st = ensure(ctx, B_PIXACC, (size_t)n_pix * 24)) != RT_OK) return st;
-		double* pixacc = (double*)ctx->buf[B_PIXACC];
-		CK(cudaMemsetAsync(pixacc, 0, (size_t)n_pix * 24, ctx->stream));
+		if ((st = ensure(ctx, B_PIXACC, (size_t)n_pix * RT_ACC_BYTES)) != RT_OK) return st;
+		long long* pixacc = (long long*)ctx->buf[B_PIXACC];
+		CK(cudaMemsetAsync(pixacc, 0, (size_t)n_pix * RT_ACC_BYTES, ctx->stream));
 		if ((st = ensure(ctx, B_REG_A, (size_t)n_pix * sizeof(Region))) != RT_OK) return st;
 		int cur = B_REG_A, nxt = B_REG_B;
 		long long n_regions = n_pix;
@@ -803,7 +816,6 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 			if (n_samples > 0x7fffffffll) { ctx->error = "too many adaptive samples for one launch"; return RT_ERR_UNSUPPORTED; }
 			if ((st = ensure(ctx, B_XS, (size_t)n_samples * 8)) != RT_OK) return st;
 			if ((st = ensure(ctx, B_YS, (size_t)n_samples * 8)) != RT_OK) return st;
-			if ((st = ensure(ctx, B_ACCUM, (size_t)n_samples * 24)) != RT_OK) return st;
 			if ((st = ensure(ctx, nxt, (size_t)n_regions * 4 * sizeof(Region))) != RT_OK) return st;
 			k_adapt_samples<<<blocks_for(n_samples, 256), 256, 0, ctx->stream>>>((const Region*)ctx->buf[cur], n_regions, N, (double*)ctx->buf[B_XS], (double*)ctx->buf[B_YS]);
 			ctx->launches++;
@@ -811,12 +823,11 @@ rt_status rt_render_device(rt_ctx* ctx, const rt_params* p, int w, int h, int pa
 			L.src = SRC_XY;
 			L.xs = (const double*)ctx->buf[B_XS];
 			L.ys = (const double*)ctx->buf[B_YS];
-			L.accum = (double*)ctx->buf[B_ACCUM];
 			L.n_slots = n_samples * A.lenses;
-			CK(cudaMemsetAsync(L.accum, 0, (size_t)n_samples * 24, ctx->stream));
+			if ((st = prepare_accum(ctx, L, B_ACCUM, B_BASE, n_samples)) != RT_OK) return st;
 			CK(cudaMemsetAsync(next_count, 0, 8, ctx->stream));
 			if ((st = launch_wave(ctx, L)) != RT_OK) return st;
-			k_adapt_resolve<<<blocks_for(n_regions, 256), 256, 0, ctx->stream>>>((const Region*)ctx->buf[cur], n_regions, N, L.accum, *p, pixacc,
+			k_adapt_resolve<<<blocks_for(n_regions, 256), 256, 0, ctx->stream>>>((const Region*)ctx->buf[cur], n_regions, N, L.accum, L.base, *p, pixacc,
 			                                                                  (Region*)ctx->buf[nxt], next_count, (unsigned long long)n_regions * 4);
 			ctx->launches++;
 			CK(cudaGetLastError());
@@ -933,7 +944,6 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 	}
 	if ((st = ensure(ctx, B_XS, (size_t)n * 8)) != RT_OK) return st;
 	if ((st = ensure(ctx, B_YS, (size_t)n * 8)) != RT_OK) return st;
-	if ((st = ensure(ctx, B_ACCUM, (size_t)n * 24)) != RT_OK) return st;
 	if ((st = ensure(ctx, B_PIXACC, (size_t)n * 24)) != RT_OK) return st;
 	CK(cudaMemcpyAsync(ctx->buf[B_XS], xs.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaMemcpyAsync(ctx->buf[B_YS], ys.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
@@ -949,21 +959,18 @@ rt_status rt_trace_pixels(rt_ctx* ctx, const rt_params* p, int w, int h, const i
 	A.depth = p->depth;
 	A.xs = (const double*)ctx->buf[B_XS];
 	A.ys = (const double*)ctx->buf[B_YS];
-	A.accum = (double*)ctx->buf[B_ACCUM];
 	A.n_slots = (long long)n * A.lenses;
-	CK(cudaMemsetAsync(A.accum, 0, (size_t)n * 24, ctx->stream));
+	if ((st = prepare_accum(ctx, A, B_ACCUM, B_BASE, n)) != RT_OK) return st;
 	if ((st = launch_wave(ctx, A)) != RT_OK) return st;
-	double* accum2 = nullptr;
+	PoolArgs A2 = A;
+	A2.accum = nullptr;
+	A2.base = nullptr;
 	if (p->anaglyph) {
-		if ((st = ensure(ctx, B_ACCUM2, (size_t)n * 24)) != RT_OK) return st;
-		accum2 = (double*)ctx->buf[B_ACCUM2];
-		CK(cudaMemsetAsync(accum2, 0, (size_t)n * 24, ctx->stream));
-		PoolArgs A2 = A;
-		A2.accum = accum2;
+		if ((st = prepare_accum(ctx, A2, B_ACCUM2, B_BASE2, n)) != RT_OK) return st;
 		A2.eye_shift = 0.25;
 		if ((st = launch_wave(ctx, A2)) != RT_OK) return st;
 	}
-	k_sample_values<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(A.accum, accum2, n, *p, (double*)ctx->buf[B_PIXACC]);
+	k_sample_values<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(A.accum, A.base, A2.accum, A2.base, n, *p, (double*)ctx->buf[B_PIXACC]);
 	ctx->launches++;
 	CK(cudaGetLastError());
 	CK(cudaMemcpyAsync(rgb_out, ctx->buf[B_PIXACC], (size_t)n * 24, cudaMemcpyDeviceToHost, ctx->stream));
@@ -994,7 +1001,6 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
 		CK(cudaMemcpyAsync(hits_out, ctx->buf[B_HITS], (size_t)n * sizeof(rt_hit), cudaMemcpyDeviceToHost, ctx->stream));
 	}
 	if (rgb_out) {
-		if ((st = ensure(ctx, B_ACCUM, (size_t)n * 24)) != RT_OK) return st;
 		PoolArgs A;
 		std::memset(&A, 0, sizeof(A));
 		A.prm = *p;
@@ -1004,11 +1010,14 @@ rt_status rt_trace_rays(rt_ctx* ctx, const rt_params* p, const rt_ray* rays, int
 		A.n_parts = 1;
 		A.depth = depth;
 		A.rays = (const rt_ray*)ctx->buf[B_RAYS];
-		A.accum = (double*)ctx->buf[B_ACCUM];
 		A.n_slots = n;
-		CK(cudaMemsetAsync(A.accum, 0, (size_t)n * 24, ctx->stream));
+		if ((st = prepare_accum(ctx, A, B_ACCUM, B_BASE, n)) != RT_OK) return st;
 		if ((st = launch_wave(ctx, A)) != RT_OK) return st;
-		CK(cudaMemcpyAsync(rgb_out, A.accum, (size_t)n * 24, cudaMemcpyDeviceToHost, ctx->stream));
+		if ((st = ensure(ctx, B_PIXACC, (size_t)n * 24)) != RT_OK) return st;
+		k_accum_values<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(A.accum, A.base, n, (double*)ctx->buf[B_PIXACC]);
+		ctx->launches++;
+		CK(cudaGetLastError());
+		CK(cudaMemcpyAsync(rgb_out, ctx->buf[B_PIXACC], (size_t)n * 24, cudaMemcpyDeviceToHost, ctx->stream));
 	}
 	return read_stats(ctx, nullptr, 0.f);
 }

@@ -10,6 +10,7 @@
 #define RT_COUNT_WORK 1
 #include "rt_shade.cuh"
 #include "rt_derive.hpp"
+#include "rt_accum.cuh"
 
 using namespace rtd;
 
@@ -240,6 +241,21 @@ int sim_walk_lengths(const void* arena, const rt_params* prm, int w, int h, int 
 			}
 	}
 	return 0;
+}
+
+// rt_accum.cuh on the host: the terms xs[0..n) split into limbs, the limbs added as integers in the given order
+// (any order gives the same limbs), the total read back.  limbs_out (optional) = {limb 0, limb 1}.
+double sim_acc_sum(const double* xs, int n, long long* limbs_out)
+{
+	unsigned long long l0 = 0, l1 = 0;
+	for (int k = 0; k < n; k++) {
+		long long lo, hi;
+		acc_split(xs[k], lo, hi);
+		l0 += (unsigned long long)lo;
+		l1 += (unsigned long long)hi;
+	}
+	if (limbs_out) { limbs_out[0] = (long long)l0; limbs_out[1] = (long long)l1; }
+	return acc_merge((long long)l0, (long long)l1);
 }
 
 } // extern "C"

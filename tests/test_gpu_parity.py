@@ -400,13 +400,9 @@ def test_small_wave_width_spills(rtlib, oracle_mod, scene_dir, scene, monkeypatc
 
 
 def _assert_same_frame(a, b):
-    """Two device renderings of the same pixels.  A sample's terms are added with FP64 atomics in launch
-    order, so a channel that lies exactly on a truncation boundary (flat regions of a material colour such as
-    0.6 * 255 = 153.0) may come out one step apart: at most 1/255 on at most 1e-5 of the pixels
-    (measured: 8 of 4.2 M pixels for C4 with adaptive AA, 0 for the other configurations)."""
-    diff = np.abs(a.astype(np.int16) - b.astype(np.int16)).max(axis=-1)
-    assert diff.max() <= 1, int(diff.max())
-    assert (diff > 0).mean() <= 1e-5, int((diff > 0).sum())
+    """Two device renderings of the same pixels are the same bytes: a sample's terms are added as integer limbs
+    (csrc/device/rt_accum.cuh), so neither launch order nor partitioning nor chunking can move a last bit."""
+    assert np.array_equal(a, b), int((a != b).any(axis=-1).sum())
 
 
 @pytest.mark.parametrize("gen,w,h_expect,depth,win", [("dragon", 1920, 1080, 5, 96), ("mixed", 7680, 4320, 8, 64)])
@@ -588,6 +584,47 @@ def test_adaptive_termination_all_scenes(rtlib, oracle_mod, ctx, scene_path, sce
     # and the switch really prunes: fewer secondary rays than without it (where the scene has any)
     _, full_st = ctx.render(rtlib.Params.default(depth=5), w, h)
     assert dev_st.reflection_rays + dev_st.refraction_rays <= full_st.reflection_rays + full_st.refraction_rays
+
+
+def test_renderings_are_bit_identical_in_any_launch_order(rtlib, ctx, scene_dir, monkeypatch):
+    """The order in which rays retire differs from run to run (queue slots are handed out atomically) and with every launch
+    setting; a sample's colour must not.  The FP64 sample values of rt_trace_pixels and whole frames (plain, adaptive AA,
+    whose pixel sums are limbs too, and adaptive termination on the pool kernel) are compared bit for bit between repeated
+    calls on one context and contexts that launch differently: coherence sort forced on for every round (threshold 1024
+    rays instead of 2^20), no sort and one shadow kernel instead of the any-hit pair, 8192-slot waves with 4096-sample chunks."""
+    settings = ({"RT_B200_SORTMIN": "1024"},
+                {"RT_B200_SORT": "0", "RT_B200_SORTC": "0", "RT_B200_ANYHIT": "0", "RT_B200_SPARSE": "0"},
+                {"RT_B200_WAVE": "8192", "RT_B200_CHUNK": "4096"})
+    others = []
+    try:
+        for env in settings:
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            others.append(rtlib.Context(0))
+            for k in env:
+                monkeypatch.delenv(k)
+        rng = np.random.default_rng(11)
+        for scene, depth in (("hitchcock.ray", 5), ("prims_mixed.ray", 6), ("dragon_small.ray", 4)):
+            arena = rtlib.load_ray_file(str(scene_dir / scene))
+            ctx.upload(arena)
+            for c in others:
+                c.upload(arena)
+            w, h = 220, 170
+            ij = rng.integers(0, 170, size=(4000, 2)).astype(np.int32)
+            for kw in (dict(), dict(aa_mode=2, aa_samples=4, aa_thresh=0.02), dict(aterm_thresh=0.05)):
+                p = rtlib.Params.default(depth=depth, **kw)
+                frame0, st0 = ctx.render(p, w, h)
+                vals0 = ctx.trace_pixels(p, w, h, ij) if not kw else None
+                for c in [ctx, ctx] + others:
+                    frame, st = c.render(p, w, h)
+                    assert np.array_equal(frame, frame0), (scene, kw)
+                    assert st.rays == st0.rays
+                    if vals0 is not None:
+                        vals = c.trace_pixels(p, w, h, ij)
+                        assert np.array_equal(vals.view(np.uint64), vals0.view(np.uint64)), (scene, kw)
+    finally:
+        for c in others:
+            c.close()
 
 
 def test_chunked_frame_is_the_same_frame(rtlib, ctx, scene_dir, monkeypatch):

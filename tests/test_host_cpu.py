@@ -375,3 +375,42 @@ def test_overlapping_objects_mode_has_no_reference_result(oracle_mod, ref_scene_
                          capture_output=True, text=True).stdout
     body = dis.split("<isect::checkObj(isect const&, isect const&)>:")[1].split("\n\n")[0]
     assert "call" in body and "ret" not in body, body
+
+
+def test_colour_accumulator_limbs(hostsim):
+    """csrc/device/rt_accum.cuh on the host: a sample's terms are held as two integer limbs per channel so that the total does
+    not depend on the order they arrive in.  One term >= 2^-16 reads back as itself (authored constants such as 0.6 or 0.2 sit
+    exactly on a byte boundary: 255 * 0.2 must stay 51.000000000000004 -> 51); a sum of such terms is the correctly rounded
+    exact sum (checked with rationals); smaller terms are rounded at 2^-68; the limbs of a permuted list are identical; NaN adds
+    nothing and infinities clamp to +-2^38."""
+    from fractions import Fraction
+    hostsim.sim_acc_sum.restype = ctypes.c_double
+    hostsim.sim_acc_sum.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+
+    def acc(xs):
+        a = np.ascontiguousarray(xs, dtype=np.float64)
+        limbs = np.zeros(2, dtype=np.int64)
+        return hostsim.sim_acc_sum(a.ctypes.data, len(a), limbs.ctypes.data), limbs
+
+    rng = np.random.default_rng(5)
+    for x in list(rng.uniform(-4, 4, 2000)) + [0.6, 0.2, 1 / 3, 2.0 ** -16, -2.0 ** -16, 1.0, 255.0, 1e3, 2.0 ** 37, -0.1]:
+        if abs(x) >= 2.0 ** -16:
+            assert acc([x])[0] == x
+    assert int(255.0 * acc([0.2])[0]) == 51 and int(255.0 * acc([0.6])[0]) == 153
+    for x in rng.uniform(-1, 1, 2000) * 2.0 ** rng.integers(-80, -16, 2000):
+        assert abs(acc([x])[0] - x) <= 2.0 ** -69
+    for _ in range(2000):
+        n = int(rng.integers(2, 60))
+        xs = rng.uniform(-1, 1, n) * 2.0 ** rng.integers(-15, 8, n)
+        assert acc(xs)[0] == float(sum(Fraction(float(x)) for x in xs))
+    xs = rng.uniform(-1, 1, 500) * 2.0 ** rng.integers(-90, 8, 500)
+    v0, l0 = acc(xs)
+    assert abs(v0 - float(sum(Fraction(float(x)) for x in xs))) <= 500 * 2.0 ** -69
+    for _ in range(20):
+        v, l = acc(rng.permutation(xs))
+        assert v == v0 and np.array_equal(l, l0)
+    assert acc([1.0, -1.0])[0] == 0.0 and acc([1.0, 2.0 ** -60, -1.0])[0] == 2.0 ** -60
+    assert acc([0.6, 0.6, 0.6])[0] == 0.6 + 0.6 + 0.6
+    assert acc([float("nan"), 0.25])[0] == 0.25
+    assert acc([float("inf")])[0] == 2.0 ** 38 and acc([-1e300])[0] == -2.0 ** 38
+    assert acc([0.0, -0.0, 5e-324])[0] == 0.0

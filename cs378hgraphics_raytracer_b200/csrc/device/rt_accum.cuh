@@ -10,8 +10,8 @@
 // and a term is split into its two limb parts and added with integer atomics (no return value: RED.ADD.64).  Integer
 // addition is associative and commutative, so the limbs - and every frame byte derived from them - are the same for any
 // launch order, queue order, number of partitions or GPUs.  Reading a channel rounds the exact limb sum to the nearest
-// double once.  Twice the atomics of a plain FP64 add: k_wave_shade therefore STORES the one term per sample that needs no
-// atomic at all (the camera ray's, see acc_read3) - A/B in profiles/r2_variants.txt.
+// double once.  Twice the atomics of a plain FP64 add: k_wave_shade therefore STORES the terms that need no atomic at all
+// (each camera ray's own, see acc_read3) - A/B in profiles/r2_variants.txt.
 //
 //  - limb 1 holds each term rounded to a multiple of 2^-24 and limb 0 the rest (|.| <= 2^-25, 44 bits); the other 20
 //    bits of each limb are head room, so 2^19 terms of one sample cannot overflow a limb whatever their signs
@@ -102,21 +102,22 @@ __device__ __forceinline__ void acc_add(long long* ch, double x)
 }
 #endif
 RT_HD double acc_read(const long long* ch) { return acc_merge(ch[0], ch[1]); }
-// One sample's colour.  `base` (optional, 3 doubles per sample) is a term that was STORED rather than added - the camera
-// ray's own term: a sample has exactly one camera ray when there is no depth of field, so its term needs no atomic - and
-// joins the limbs here, as one more integer addition.
-RT_HD d3 acc_read3(const long long* acc, const double* base, long long sample)
+// One sample's colour.  `base` (optional, 3 doubles per camera-ray slot, `lenses` slots per sample) holds the terms that were
+// STORED rather than added - each camera ray's own term: the slot is its alone, so the term needs no atomic - and they join
+// the limbs here, as more integer additions.
+RT_HD d3 acc_read3(const long long* acc, const double* base, int lenses, long long sample)
 {
 	const long long* a = acc + RT_ACC_STRIDE * sample;
 	double v[3];
 	for (int c = 0; c < 3; c++) {
 		unsigned long long l0 = (unsigned long long)a[2 * c], l1 = (unsigned long long)a[2 * c + 1];
-		if (base) {
-			long long lo, hi;
-			acc_split(base[3 * sample + c], lo, hi);
-			l0 += (unsigned long long)lo;
-			l1 += (unsigned long long)hi;
-		}
+		if (base)
+			for (int l = 0; l < lenses; l++) {
+				long long lo, hi;
+				acc_split(base[3 * (sample * lenses + l) + c], lo, hi);
+				l0 += (unsigned long long)lo;
+				l1 += (unsigned long long)hi;
+			}
 		v[c] = acc_merge((long long)l0, (long long)l1);
 	}
 	return mk3(v[0], v[1], v[2]);

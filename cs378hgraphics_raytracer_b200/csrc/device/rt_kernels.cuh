@@ -41,7 +41,7 @@ struct PoolArgs {
 	const double* ys;
 	const rt_ray* rays; // SRC_RAYS
 	long long* accum;   // RT_ACC_STRIDE limbs per sample (rt_accum.cuh)
-	double* base;       // 3 doubles per sample: the camera ray's own term, stored instead of added (nullptr with depth of field: several camera rays per sample)
+	double* base;       // 3 doubles per camera-ray slot (`lenses` per sample): that ray's own term, stored instead of added
 	unsigned long long* cursor;
 	unsigned long long* stats; // camera, reflection, refraction, shadow, overflow flag
 	double* pool_d;     // per warp: RT_POOL_DOUBLES x cap doubles
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(128) k_hits(const DScene S, const rt_ray* rays
 // RayTracer::trace's tail for one sample (RayTracer.cpp:74-78): mean over the lens rays, clamp
 __device__ __forceinline__ d3 sample_value(const long long* accum, const double* base, long long sample, const rt_params& prm)
 {
-	d3 c = acc_read3(accum, base, sample);
+	d3 c = acc_read3(accum, base, prm.dof_on ? prm.dof_divs + 1 : 1, sample);
 	if (prm.dof_on) c = c * (1.0 / (prm.dof_divs + 1.0));
 	return gclamp(c, 0.0, 1.0);
 }
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(256) k_adapt_store(const PoolArgs A, long long
 	int pi, pj;
 	double x, y;
 	if (!grid_sample(A, pix, pi, pj, x, y)) return;
-	store_pixel(fb, A.w, pi, pj, acc_read3(pix_accum, nullptr, pix));
+	store_pixel(fb, A.w, pi, pj, acc_read3(pix_accum, nullptr, 1, pix));
 }
 
 } // namespace rtd
@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(256) k_accum_values(const long long* accum, co
 {
 	const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (k >= n) return;
-	const d3 c = acc_read3(accum, base, k);
+	const d3 c = acc_read3(accum, base, 1, k);
 	out[3 * k] = c.x;
 	out[3 * k + 1] = c.y;
 	out[3 * k + 2] = c.z;

@@ -65,11 +65,11 @@ __device__ __forceinline__ void accumulate(long long* accum, int sample, const d
 	if (c.z != 0.0) acc_add(acc + 4, c.z);
 }
 
-// a ray's own term (emission + ambient, or the background): the camera ray's is the only one of its sample, a plain store
-__device__ __forceinline__ void add_term(const PoolArgs& A, int sample, bool camera, const d3& c)
+// a ray's own term (emission + ambient, or the background): a camera ray's goes to the slot only it owns, a plain store
+__device__ __forceinline__ void add_term(const PoolArgs& A, int sample, bool camera, int lens, const d3& c)
 {
 	if (camera && A.base) {
-		double* b = A.base + 3ll * sample;
+		double* b = A.base + 3ll * ((long long)sample * A.lenses + lens);
 		b[0] = c.x; b[1] = c.y; b[2] = c.z;
 	} else {
 		accumulate(A.accum, sample, c);

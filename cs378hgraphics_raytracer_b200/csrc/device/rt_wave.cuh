@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS) k_wave_gen(const __grid_const
 	Q.store_v(3, q, rd);
 	Q.store_v(6, q, mk3(1.0, 1.0, 1.0));
 	Q.store_v(9, q, mk3(1.0, 1.0, 1.0));
-	Q.store_meta(q, (int)smp, pack_meta(A.depth, 0, ok ? KIND_CAMERA : KIND_DEAD, 0));
+	Q.store_meta(q, (int)smp, pack_meta(A.depth, 0, ok ? KIND_CAMERA : KIND_DEAD, lens)); // a camera ray carries its lens index where a shadow ray has its light
 }
 
 // Per-block copy of the scene tree's top table into shared memory (rt_scene.cuh: RT_REF_TOP); every thread of the block takes
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 		else n_refr = 1;
 		const double t = H.t[k];
 		if (t < 0.0) {
-			add_term(A, sample, kind == KIND_CAMERA, weight * miss_colour(S, A.prm, rd));
+			add_term(A, sample, kind == KIND_CAMERA, meta >> 16, weight * miss_colour(S, A.prm, rd));
 		} else {
 			const int2 of = H.of[k];
 			h.obj = of.x;
@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(RT_WAVE_THREADS, RT_SHADE_MINB) k_wave_shade(c
 			finalize_hit(S, ro, rd, h);
 			w = apply_att(weight, Q.load_v(9, q), (meta >> 8) & 15, h.t);
 			eval_material(S, h, me);
-			add_term(A, sample, kind == KIND_CAMERA, w * (me.ke + me.ka * ld3(S.glob.ambient)));
+			add_term(A, sample, kind == KIND_CAMERA, meta >> 16, w * (me.ke + me.ka * ld3(S.glob.ambient)));
 			hitP = ro + h.t * rd;
 			lit = true;
 			spawn_children(me, h, ro, rd, w, (meta & 255) - 1, kid, has_refl, has_refr);

@@ -432,20 +432,17 @@ rt_status read_stats(rt_ctx* ctx, rt_stats* stats, float ms)
 
 } // namespace
 
-// zeroed sample accumulators for one launch: the limbs (rt_accum.cuh) and, when a sample has exactly one camera ray,
-// the array that ray's own term is stored in
+// zeroed sample accumulators for one launch: the limbs (rt_accum.cuh) and the array the camera rays' own terms are stored in
 static rt_status prepare_accum(rt_ctx* ctx, PoolArgs& A, int b_accum, int b_base, long long n_samples)
 {
 	rt_status st;
 	if ((st = ensure(ctx, b_accum, (size_t)n_samples * RT_ACC_BYTES)) != RT_OK) return st;
 	A.accum = (long long*)ctx->buf[b_accum];
 	CK(cudaMemsetAsync(A.accum, 0, (size_t)n_samples * RT_ACC_BYTES, ctx->stream));
-	A.base = nullptr;
-	if (A.lenses == 1) {
-		if ((st = ensure(ctx, b_base, (size_t)n_samples * 24)) != RT_OK) return st;
-		A.base = (double*)ctx->buf[b_base];
-		CK(cudaMemsetAsync(A.base, 0, (size_t)n_samples * 24, ctx->stream));
-	}
+	const size_t slots = (size_t)n_samples * (size_t)A.lenses;
+	if ((st = ensure(ctx, b_base, slots * 24)) != RT_OK) return st;
+	A.base = (double*)ctx->buf[b_base];
+	CK(cudaMemsetAsync(A.base, 0, slots * 24, ctx->stream));
 	return RT_OK;
 }
 

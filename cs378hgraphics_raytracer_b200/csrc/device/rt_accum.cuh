@@ -78,8 +78,11 @@ RT_HD double acc_merge(long long lo, long long hi)
 		top = a0;
 		shift = 0;
 	} else {
-		int lz = 0;
-		for (unsigned long long t = a1; !(t >> 63); t <<= 1) lz++;
+#ifdef __CUDA_ARCH__
+		const int lz = __clzll((long long)a1);
+#else
+		const int lz = __builtin_clzll(a1);
+#endif
 		if (lz == 0) {
 			top = a1 | (a0 != 0 ? 1ull : 0ull);
 		} else {
@@ -88,7 +91,11 @@ RT_HD double acc_merge(long long lo, long long hi)
 		}
 		shift = 64 - lz;
 	}
-	const double v = ldexp((double)top, shift + RT_ACC_UNIT_EXP);
+	// * 2^(shift - 68): an exact power of two built from its exponent field (0 <= shift <= 64: always a normal number)
+	const unsigned long long pw = (unsigned long long)(1023 + shift + RT_ACC_UNIT_EXP) << 52;
+	double scale;
+	memcpy(&scale, &pw, 8);
+	const double v = (double)top * scale;
 	return neg ? -v : v;
 }
 

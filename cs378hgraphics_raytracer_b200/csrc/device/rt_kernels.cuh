@@ -10,7 +10,7 @@
 //     cursor, traces + shades one ray per lane, and pushes the reflection/refraction children of
 //     all lanes back with a warp-scan compaction.
 // The recursion's return value becomes a forward weight (see RayTask), so a ray's contribution is
-// added to its camera sample's accumulator (FP64 atomics) the moment it is shaded and no parent
+// added to its camera sample's accumulator (integer limbs, rt_accum.cuh) the moment it is shaded and no parent
 // ever waits for a child.  Shadow rays are traced inline by the shading lane.
 #pragma once
 #include <cuda_runtime.h>

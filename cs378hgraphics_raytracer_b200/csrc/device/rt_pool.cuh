@@ -76,14 +76,6 @@ __device__ __forceinline__ void add_term(const PoolArgs& A, int sample, bool cam
 	}
 }
 
-// the same as a real call, for kernels whose register budget is the tighter constraint (RT_ACC_COLD_SHADOW, A/B in profiles/r2_variants.txt)
-__device__ __noinline__ void accumulate_cold(long long* accum, int sample, const d3& c) { accumulate(accum, sample, c); }
-#ifdef RT_ACC_COLD_SHADOW
-#define accumulate_shadow accumulate_cold
-#else
-#define accumulate_shadow accumulate
-#endif
-
 // DEFER = true : shadow rays are pool entries (normal case)
 // DEFER = false: shadow rays traced inline by the shading lane (adaptive termination needs the
 //                shadowed colour before deciding to recurse, RayTracer.cpp:124-125)

@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 		traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B, 0, top);
 		if (shadow_walk(st, B, Lt, rd, A.prm)) break;
 	}
-	accumulate_shadow(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
+	accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
 }
 
 // ---- stage 3, two-kernel form: decide by classification, walk completely only what needs it ---------------------------
@@ -514,7 +514,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_ANY_MINB) k_wave_shadow_a
 		}
 		if (!(Y.fl & SH_DEAD) && !Y.settled_by_exit()) {
 			if (Y.fl & SH_OTHER) complex_ray = true;
-			else accumulate_shadow(A.accum, SQ.i[k], SQ.load_v(6, k)); // nothing before the light: attenuation exactly (1,1,1)
+			else accumulate(A.accum, SQ.i[k], SQ.load_v(6, k)); // nothing before the light: attenuation exactly (1,1,1)
 		}
 	}
 	const long long s = wave_reserve(complex_ray, (1u << lane) - 1u, &cnt->n_complex[parity]);
@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, RT_SHADOW_MINB) k_wave_shado
 			traverse<true, TRAV_SHADOW>(S, ro, rd, TRAV_SHADOW, unused, B, 0, top);
 			if (shadow_walk(st, B, Lt, rd, A.prm)) break;
 		}
-		accumulate_shadow(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
+		accumulate(A.accum, SQ.i[k], SQ.load_v(6, k) * st.sattn);
 	}
 }
 

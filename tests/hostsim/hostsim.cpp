@@ -258,4 +258,20 @@ double sim_acc_sum(const double* xs, int n, long long* limbs_out)
 	return acc_merge((long long)l0, (long long)l1);
 }
 
+// acc_read3 as the resolve kernels call it: one sample's red channel from its limbs (the added terms) and the `lenses`
+// stored camera-ray terms of its slots
+double sim_acc_read(const double* added, int n_added, const double* stored, int lenses)
+{
+	long long acc[RT_ACC_STRIDE] = {0, 0, 0, 0, 0, 0};
+	for (int k = 0; k < n_added; k++) {
+		long long lo, hi;
+		acc_split(added[k], lo, hi);
+		acc[0] = (long long)((unsigned long long)acc[0] + (unsigned long long)lo);
+		acc[1] = (long long)((unsigned long long)acc[1] + (unsigned long long)hi);
+	}
+	std::vector<double> base(3 * (size_t)lenses, 0.0);
+	for (int l = 0; l < lenses; l++) base[3 * l] = stored[l];
+	return acc_read3(acc, lenses ? base.data() : nullptr, lenses, 0).x;
+}
+
 } // extern "C"

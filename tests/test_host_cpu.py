@@ -414,3 +414,14 @@ def test_colour_accumulator_limbs(hostsim):
     assert acc([float("nan"), 0.25])[0] == 0.25
     assert acc([float("inf")])[0] == 2.0 ** 38 and acc([-1e300])[0] == -2.0 ** 38
     assert acc([0.0, -0.0, 5e-324])[0] == 0.0
+    # the resolve side: terms that were added (limbs) plus the camera rays' stored terms (one slot per lens ray) = one exact sum
+    hostsim.sim_acc_read.restype = ctypes.c_double
+    hostsim.sim_acc_read.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
+    for lenses in (0, 1, 6):
+        added = np.ascontiguousarray(rng.uniform(0, 1, 40) * 2.0 ** rng.integers(-12, 2, 40))
+        stored = np.ascontiguousarray(rng.uniform(0, 1, max(lenses, 1)))
+        got = hostsim.sim_acc_read(added.ctypes.data, len(added), stored.ctypes.data, lenses)
+        want = float(sum(Fraction(float(x)) for x in list(added) + list(stored[:lenses])))
+        assert got == want
+    one = np.array([0.6])
+    assert hostsim.sim_acc_read(None, 0, one.ctypes.data, 1) == 0.6  # a camera ray that hits a flat emitter: that very double

@@ -19,7 +19,7 @@
 
 namespace rtd {
 
-enum { SRC_GRID = 0, SRC_XY = 1, SRC_RAYS = 2 };
+enum { SRC_GRID = 0, SRC_XY = 1, SRC_RAYS = 2, SRC_QUEUE = 3 };
 #define RT_TILE 32
 #define RT_TILE_PIX (RT_TILE * RT_TILE)
 #define RT_CHUNK 32
@@ -40,6 +40,9 @@ struct PoolArgs {
 	const double* xs;   // SRC_XY: sample window coordinates
 	const double* ys;
 	const rt_ray* rays; // SRC_RAYS
+	const double* q_d;  // SRC_QUEUE (k_trace_pool finishing a frame from the wavefront's queue): the RayQueue's arrays and capacity
+	const int* q_i;
+	long long q_cap;
 	long long* accum;   // RT_ACC_STRIDE limbs per sample (rt_accum.cuh)
 	double* base;       // 3 doubles per camera-ray slot (`lenses` per sample): that ray's own term, stored instead of added
 	unsigned long long* cursor;

@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(RT_POOL_THREADS, RT_POOL_MINB) k_trace_pool(co
 	// the ray this lane is working on
 	bool has_task = false;
 	d3 ro, rd;
-	int sample = 0, meta = 0, slot = -1; // slot: where the rest of the entry still lies (-1: fresh camera ray)
+	int sample = 0, meta = 0, slot = -1; // slot: where the rest of the entry still lies (-1: fresh camera ray, < -1: entry -2 - slot of the source queue)
 	unsigned n_cam = 0, n_refl = 0, n_refr = 0, n_shadow = 0, overflow = 0;
 
 	for (;;) {
@@ -133,7 +133,16 @@ __global__ void __launch_bounds__(RT_POOL_THREADS, RT_POOL_MINB) k_trace_pool(co
 					const long long smp = s / A.lenses;
 					const int lens = (int)(s % A.lenses);
 					bool ok = true;
-					if (A.src == SRC_RAYS) {
+					if (A.src == SRC_QUEUE) {
+						// a ray some wavefront round left in its queue (rt_wave.cuh: RayQueue, 12 doubles + sample + meta)
+						ro = mk3(A.q_d[0 * A.q_cap + s], A.q_d[1 * A.q_cap + s], A.q_d[2 * A.q_cap + s]);
+						rd = mk3(A.q_d[3 * A.q_cap + s], A.q_d[4 * A.q_cap + s], A.q_d[5 * A.q_cap + s]);
+						sample = A.q_i[s];
+						meta = A.q_i[A.q_cap + s];
+						slot = -2 - (int)s; // its weight and attenuation are still there
+						has_task = true;
+						ok = false;         // (nothing more to set up below)
+					} else if (A.src == SRC_RAYS) {
 						ro = ld3(A.rays[s].p);
 						rd = ld3(A.rays[s].d);
 					} else {
@@ -194,6 +203,11 @@ __global__ void __launch_bounds__(RT_POOL_THREADS, RT_POOL_MINB) k_trace_pool(co
 		if (has_task && mode == TRAV_CLOSEST) {
 			d3 weight = mk3(1.0, 1.0, 1.0), att_kt = mk3(1.0, 1.0, 1.0);
 			if (slot >= 0) { weight = P.load_v(6, slot); att_kt = P.load_v(9, slot); }
+			else if (slot < -1) {
+				const long long qi = -2 - slot;
+				weight = mk3(A.q_d[6 * A.q_cap + qi], A.q_d[7 * A.q_cap + qi], A.q_d[8 * A.q_cap + qi]);
+				att_kt = mk3(A.q_d[9 * A.q_cap + qi], A.q_d[10 * A.q_cap + qi], A.q_d[11 * A.q_cap + qi]);
+			}
 			if (kind == KIND_CAMERA) n_cam++;
 			else if (kind == KIND_REFL) n_refl++;
 			else n_refr++;

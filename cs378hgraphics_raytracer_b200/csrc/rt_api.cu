@@ -55,6 +55,7 @@ struct rt_ctx {
 	long long any_n[2] = {0, 0};           // rays of the any-hit launch in flight per round parity (0: that launch was one-kernel)
 	int any_round[2] = {0, 0};             // ... and the round it belongs to
 	bool shadow_two = true;                // RT_B200_ANYHIT=0: one shadow kernel (k_wave_shadow) instead of any-hit classification + complete walk of the rest
+	long long tail_rays = 0;               // a round of at most this many rays, with nothing else left to start, is finished by ONE launch of the fused kernel (RT_B200_TAIL; 0 = off)
 	long long sort_min = RT_SORT_MIN;      // rounds with fewer rays are walked in queue order (RT_B200_SORTMIN)
 	long long chunk_samples = 1ll << 28;   // camera samples per launch of the grid path (RT_B200_CHUNK; a frame above it is rendered in chunks of tiles)
 	bool sparse_small = true;              // RT_B200_SPARSE=0: small rounds are launched densely (32 rays per warp) like large ones
@@ -154,6 +155,7 @@ rt_status make_queue(rt_ctx* ctx, int bd, int bi, long long cap, int nd, RayQueu
 }
 
 rt_status launch_pool(rt_ctx* ctx, PoolArgs& A);
+rt_status launch_tail(rt_ctx* ctx, const PoolArgs& A, const RayQueue& q, long long n);
 
 cudaEvent_t next_event(rt_ctx* ctx)
 {
@@ -246,6 +248,15 @@ rt_status launch_wave(rt_ctx* ctx, PoolArgs& A)
 	A.stats = cnt->stats;
 	long long cur_n = 0, sp_n = 0, cam = 0;
 	for (;;) {
+		// The floor of a small round is its slowest walk, paid once per stage and recursion level.  When only a few rays are
+		// left - no camera samples to start, nothing spilled - the fused persistent kernel takes the queue and carries every
+		// ray's whole subtree to the end in ONE launch (its warps keep their own LIFO pools).  Same arithmetic, and the
+		// accumulators do not care about the order: the frame is the same bytes (tests/test_gpu_parity.py).
+		if (ctx->tail_rays > 0 && cur_n > 0 && cur_n <= ctx->tail_rays && sp_n == 0 && cam >= A.n_slots) {
+			if ((st = launch_tail(ctx, A, cur, cur_n)) != RT_OK) return st;
+			ctx->rounds++;
+			break;
+		}
 		long long base = 0, m = 0;
 		long long n_kids = cur_n < W ? cur_n : W; // the batch's first n_kids rays are children of the previous round
 		if (cur_n > W) {
@@ -405,6 +416,34 @@ rt_status launch_pool(rt_ctx* ctx, PoolArgs& A)
 	return RT_OK;
 }
 
+// The rest of a frame from the wavefront's queue: k_trace_pool with the queue as its source of rays.
+rt_status launch_tail(rt_ctx* ctx, const PoolArgs& A, const RayQueue& q, long long n)
+{
+	PoolArgs T = A;
+	T.src = SRC_QUEUE;
+	T.q_d = q.d;
+	T.q_i = q.i;
+	T.q_cap = q.cap;
+	T.n_slots = n;
+	T.lenses = 1;
+	const long long warps = (long long)ctx->pool_blocks * (RT_POOL_THREADS / 32);
+	const bool defer = ctx->n_area_lights == 0; // as launch_pool: area lights are shaded inline
+	T.cap = 32 * (A.depth + 3) + (defer ? 64 * ctx->S.n_lights + 64 : 0);
+	rt_status st;
+	if ((st = ensure(ctx, B_POOL_D, (size_t)warps * T.cap * RT_POOL_DOUBLES * sizeof(double))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_POOL_I, (size_t)warps * T.cap * 2 * sizeof(int))) != RT_OK) return st;
+	T.pool_d = (double*)ctx->buf[B_POOL_D];
+	T.pool_i = (int*)ctx->buf[B_POOL_I];
+	unsigned long long* small = (unsigned long long*)ctx->buf[B_SMALL];
+	T.cursor = small + 20; // behind the wavefront's own counters (WaveCounters: 16 words) and the adaptive-AA region count
+	T.stats = small;       // the same ray counters the stage kernels add to
+	CK(cudaMemsetAsync(T.cursor, 0, sizeof(unsigned long long), ctx->stream));
+	if (defer) { STAGE(RT_STAGE_OTHER, (k_trace_pool<true><<<ctx->pool_blocks, RT_POOL_THREADS, 0, ctx->stream>>>(ctx->S, T))); }
+	else { STAGE(RT_STAGE_OTHER, (k_trace_pool<false><<<ctx->pool_blocks, RT_POOL_THREADS, 0, ctx->stream>>>(ctx->S, T))); }
+	CK(cudaGetLastError());
+	return RT_OK;
+}
+
 rt_status read_stats(rt_ctx* ctx, rt_stats* stats, float ms)
 {
 	unsigned long long h[8];
@@ -474,6 +513,7 @@ rt_status rt_create(int device, rt_ctx** out)
 	if (const char* e = getenv("RT_B200_SORT")) ctx->sort_shadow = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SORTC")) ctx->sort_closest = atoi(e) != 0;
 	if (const char* e = getenv("RT_B200_SPARSE")) ctx->sparse_small = atoi(e) != 0;
+	if (const char* e = getenv("RT_B200_TAIL")) { const long long v = atoll(e); if (v >= 0) ctx->tail_rays = v; }
 	if (const char* e = getenv("RT_B200_SORTMIN")) { const long long v = atoll(e); if (v >= 1024) ctx->sort_min = v; }
 	if (const char* e = getenv("RT_B200_CHUNK")) { const long long v = atoll(e); if (v >= 1024 && v <= (1ll << 30)) ctx->chunk_samples = v; }
 	if (const char* e = getenv("RT_B200_ANYHIT")) ctx->shadow_two = atoi(e) != 0;

@@ -588,13 +588,15 @@ def test_adaptive_termination_all_scenes(rtlib, oracle_mod, ctx, scene_path, sce
 
 def test_renderings_are_bit_identical_in_any_launch_order(rtlib, ctx, scene_dir, monkeypatch):
     """The order in which rays retire differs from run to run (queue slots are handed out atomically) and with every launch
-    setting; a sample's colour must not.  The FP64 sample values of rt_trace_pixels and whole frames (plain, adaptive AA,
+    setting - or with the engine: the fused persistent kernel can take a frame over from the wavefront's queue (RT_B200_TAIL) -;
+    a sample's colour must not.  The FP64 sample values of rt_trace_pixels and whole frames (plain, adaptive AA,
     whose pixel sums are limbs too, and adaptive termination on the pool kernel) are compared bit for bit between repeated
     calls on one context and contexts that launch differently: coherence sort forced on for every round (threshold 1024
     rays instead of 2^20), no sort and one shadow kernel instead of the any-hit pair, 8192-slot waves with 4096-sample chunks."""
     settings = ({"RT_B200_SORTMIN": "1024"},
                 {"RT_B200_SORT": "0", "RT_B200_SORTC": "0", "RT_B200_ANYHIT": "0", "RT_B200_SPARSE": "0"},
-                {"RT_B200_WAVE": "8192", "RT_B200_CHUNK": "4096"})
+                {"RT_B200_WAVE": "8192", "RT_B200_CHUNK": "4096"},
+                {"RT_B200_TAIL": "100000000"})  # every round after the first is finished by the fused kernel from the queue
     others = []
     try:
         for env in settings:

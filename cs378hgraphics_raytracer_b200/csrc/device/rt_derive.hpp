@@ -6,6 +6,7 @@
 #include <vector>
 #include "rt_arena_writer.hpp"
 #include "rt_scene.cuh"
+#include "rt_prims.cuh" // derive_primf
 
 namespace rtd {
 
@@ -13,6 +14,7 @@ struct Derived {
 	std::vector<DNode2> snodes2, mnodes2;
 	std::vector<DNode2f> snodes2f, mnodes2f;
 	std::vector<DItemBox> sboxf;
+	std::vector<DPrimF> sprimf;
 	DTree stree;
 	std::vector<DTree> mtrees;
 	std::vector<DTri> tris;
@@ -141,6 +143,12 @@ inline void derive(const rt::ArenaView& A, Derived& D)
 		for (int c = 0; c < 3; c++) { b.lo[c] = (float)objs[obj].bbox[c]; b.hi[c] = (float)objs[obj].bbox[3 + c]; }
 		b.obj = obj;
 		b.type = objs[obj].type;
+	}
+	D.sprimf.resize(D.sboxf.size());
+	for (size_t k = 0; k < D.sboxf.size(); k++) {
+		const int32_t obj = sitems[k];
+		if (obj < 0 || (uint64_t)obj >= A.count(RT_SEC_OBJECTS)) { std::memset(&D.sprimf[k], 0, sizeof(DPrimF)); continue; }
+		derive_primf(objs[obj], D.sboxf[k], D.sprimf[k]);
 	}
 }
 

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256) k_derive_nodes2f(const DNode2* in, long l
 
 // float image of the candidates' world boxes, in leaf item order (bad item indices are reported by
 // k_derive_check; their slot is left zeroed)
-__global__ void __launch_bounds__(256) k_derive_itembox(const int32_t* sitems, long long n_sitems, const rt_object* objs, long long n_obj, DItemBox* out)
+__global__ void __launch_bounds__(256) k_derive_itembox(const int32_t* sitems, long long n_sitems, const rt_object* objs, long long n_obj, DItemBox* out, DPrimF* outp)
 {
 	const long long k = (long long)blockIdx.x * 256 + threadIdx.x;
 	if (k >= n_sitems) return;
@@ -95,6 +95,11 @@ __global__ void __launch_bounds__(256) k_derive_itembox(const int32_t* sitems, l
 	b.obj = ok ? obj : 0;
 	b.type = ok ? objs[obj].type : 0;
 	out[k] = b;
+	// the object-space float test's record of the same item (rt_prims.cuh: derive_primf, the host build runs the same function)
+	DPrimF p;
+	if (ok) derive_primf(objs[obj], b, p);
+	else { for (int j = 0; j < 9; j++) p.m[j] = 0.0f; p.lc[0] = p.lc[1] = p.lc[2] = 0.0f; p.kind = 0; p.pad[0] = p.pad[1] = p.pad[2] = 0; }
+	outp[k] = p;
 }
 
 // breadth-first top table of the scene tree (rt_scene.cuh: RT_REF_TOP); one thread, at most `cap` nodes

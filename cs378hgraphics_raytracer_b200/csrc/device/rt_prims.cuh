@@ -156,6 +156,103 @@ RT_HD bool box_miss_f(const DItemBox& b, const RayF& F, float limf = INFINITY)
 	return r == 0 || (r == 1 && e > limf);
 }
 
+// ---- object-space float pre-test of a scene-level candidate (DPrimF, rt_scene.cuh) ------------------------------------------
+// The same function builds the record on the host (rt_derive.hpp) and on the device (rt_derive_dev.cuh): plain double
+// arithmetic, no contraction, so the two images are byte-identical.
+RT_HD void derive_primf(const rt_object& ob, const DItemBox& b, DPrimF& p)
+{
+	for (int k = 0; k < 9; k++) p.m[k] = 0.0f;
+	p.lc[0] = p.lc[1] = p.lc[2] = 0.0f;
+	p.kind = RT_PF_NONE;
+	p.pad[0] = p.pad[1] = p.pad[2] = 0;
+	int kind;
+	double az = 0.0; // centre of the shape's own bounding box (on the z axis)
+	switch (ob.type) {
+	case RT_OBJ_BOX: kind = RT_PF_BOX; break;           // [-0.5, 0.5]^3 (Box.cpp)
+	case RT_OBJ_SPHERE: kind = RT_PF_SPHERE; break;     // radius 1 (Sphere.cpp)
+	case RT_OBJ_SQUARE: kind = RT_PF_SQUARE; break;     // [-0.5, 0.5]^2 in z = 0 (Square.cpp)
+	case RT_OBJ_CYLINDER: kind = RT_PF_CYLINDER; az = 0.5; break; // radius 1, z in [0, 1], capped (Cylinder.cpp)
+	default: return; // trimeshes are entered, cones keep the double test (their root bookkeeping is followed literally)
+	}
+	// inverse transform: element (row r, column c) = inv[4 c + r] (rt_math.cuh: xform_point)
+	double M[9], n[3];
+	for (int r = 0; r < 3; r++) {
+		for (int c = 0; c < 3; c++) M[3 * r + c] = ob.inv[4 * c + r];
+		n[r] = (M[3 * r] * M[3 * r] + M[3 * r + 1] * M[3 * r + 1]) + M[3 * r + 2] * M[3 * r + 2];
+	}
+	// rotation x uniform scale only: rows of equal length, orthogonal (to 1e-6).  Then |m v| = s |v| for every v, no component
+	// of m v is a small difference of large terms beyond what |v| allows, and the error bounds in prim_miss_f hold.
+	const double mx = n[0] > n[1] ? (n[0] > n[2] ? n[0] : n[2]) : (n[1] > n[2] ? n[1] : n[2]);
+	const double mn = n[0] < n[1] ? (n[0] < n[2] ? n[0] : n[2]) : (n[1] < n[2] ? n[1] : n[2]);
+	if (!(mn > 1e-60) || !(mx < 1e60) || !(mx - mn <= 1e-6 * mx)) return;
+	for (int r = 0; r < 3; r++) {
+		const int q = (r + 1) % 3;
+		const double dp = (M[3 * r] * M[3 * q] + M[3 * r + 1] * M[3 * q + 1]) + M[3 * r + 2] * M[3 * q + 2];
+		if (!(dp <= 1e-6 * mx && dp >= -1e-6 * mx)) return;
+	}
+	// reference point: the centre of the item's float box, as prim_miss_f recomputes it
+	const float cf[3] = {0.5f * (b.lo[0] + b.hi[0]), 0.5f * (b.lo[1] + b.hi[1]), 0.5f * (b.lo[2] + b.hi[2])};
+	const d3 lc = xform_point(ob.inv, mk3((double)cf[0], (double)cf[1], (double)cf[2]));
+	const double l[3] = {lc.x, lc.y, lc.z - az};
+	for (int c = 0; c < 3; c++)
+		if (!(l[c] < 4.0 && l[c] > -4.0)) return; // the box centre of a unit-sized shape lies within it; anything else is left alone
+	for (int k = 0; k < 9; k++) p.m[k] = (float)M[k];
+	for (int c = 0; c < 3; c++) p.lc[c] = (float)l[c];
+	p.kind = kind;
+}
+
+// true = the LINE of the ray certainly misses the shape, so Geometry::intersect (scene.cpp:13-40: world -> object ray,
+// intersectLocal) certainly answers "no hit" whatever t range it looks at.  o, d = the world ray (double), b = the item's box.
+//  * q = o + t0 d, t0 ~ where the ray passes the box centre: a point of the ray NEAR the object, computed in double precision,
+//    so that the float numbers below are small (object-sized) whatever the distance of the ray's origin;
+//  * l = m (q - c) + lc and e = m d: the line in object space, centred on the shape's bounding box; with |l|_1 < 8 (checked;
+//    a ray through the box of a unit-sized shape passes its centre within 4.5) their components are within 6e-6 and
+//    4e-7 |e|_1 of the exact ones (four float roundings per component on terms of that size, rows of m of equal length),
+//    a cross product component (l x e)_k within 1e-5 |e|_1;
+//  * box / square / cylinder: separating axes e x u_k of a line and a box with half extents h (the cylinder's bounding box):
+//    |(l x e)_k| > h_i |e_j| + h_j |e_i|; h is widened by 2e-3 and an axis is used only if |e_i| + |e_j| > 0.05 |e|_1, which
+//    makes the widening worth >= 1e-4 |e|_1: ten times the error above (the primitives themselves accept nothing outside
+//    their shape: Box.cpp / Square.cpp / Cylinder.cpp compare against the exact extents);
+//  * sphere / cylinder: distance of the line from the centre / the axis against the radius widened the same way.
+// NaN, infinities, zero directions: every comparison is written so that they answer "false" (no certain miss).
+RT_HD bool prim_miss_f(const DPrimF& p, const DItemBox& b, const d3& o, const d3& d)
+{
+	if (p.kind == RT_PF_NONE) return false;
+	const float cx = 0.5f * (b.lo[0] + b.hi[0]), cy = 0.5f * (b.lo[1] + b.hi[1]), cz = 0.5f * (b.lo[2] + b.hi[2]);
+	const float dx = (float)d.x, dy = (float)d.y, dz = (float)d.z;
+	const float t0 = ((cx - (float)o.x) * dx + (cy - (float)o.y) * dy + (cz - (float)o.z) * dz) / (dx * dx + dy * dy + dz * dz);
+	if (!(t0 < 1e30f && t0 > -1e30f)) return false;
+	const double t = (double)t0;
+	const float qx = (float)((o.x + t * d.x) - (double)cx), qy = (float)((o.y + t * d.y) - (double)cy), qz = (float)((o.z + t * d.z) - (double)cz);
+	const float lx = (p.m[0] * qx + p.m[1] * qy + p.m[2] * qz) + p.lc[0];
+	const float ly = (p.m[3] * qx + p.m[4] * qy + p.m[5] * qz) + p.lc[1];
+	const float lz = (p.m[6] * qx + p.m[7] * qy + p.m[8] * qz) + p.lc[2];
+	const float ex = p.m[0] * dx + p.m[1] * dy + p.m[2] * dz;
+	const float ey = p.m[3] * dx + p.m[4] * dy + p.m[5] * dz;
+	const float ez = p.m[6] * dx + p.m[7] * dy + p.m[8] * dz;
+	if (!(fabsf(lx) + fabsf(ly) + fabsf(lz) < 8.0f)) return false;
+	const float ax = fabsf(ex), ay = fabsf(ey), az = fabsf(ez);
+	const float en = ax + ay + az;
+	if (!(en > 1e-30f && en < 1e30f)) return false;
+	const float kx = ly * ez - lz * ey, ky = lz * ex - lx * ez, kz = lx * ey - ly * ex; // l x e
+	const float w = 2e-3f;
+	if (p.kind == RT_PF_SPHERE) {
+		const float r = 1.0f + w;
+		return (kx * kx + ky * ky) + kz * kz > (r * r) * ((ex * ex + ey * ey) + ez * ez);
+	}
+	const bool round_xy = p.kind == RT_PF_CYLINDER;
+	const float hx = (round_xy ? 1.0f : 0.5f) + w, hy = hx, hz = (p.kind == RT_PF_SQUARE ? 0.0f : 0.5f) + w;
+	const float thr = 0.05f * en;
+	if (ay + az > thr && fabsf(kx) > hy * az + hz * ay) return true;
+	if (az + ax > thr && fabsf(ky) > hz * ax + hx * az) return true;
+	if (ax + ay > thr && fabsf(kz) > hx * ay + hy * ax) return true;
+	if (round_xy) {
+		const float exy = ex * ex + ey * ey;
+		if (exy > (thr * thr) && kz * kz > (hx * hx) * exy) return true;
+	}
+	return false;
+}
+
 // What a primitive's intersectLocal leaves in the isect (object space).
 struct LocalHit {
 	double t;

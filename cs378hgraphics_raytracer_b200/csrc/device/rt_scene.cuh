@@ -44,6 +44,20 @@ struct alignas(32) DItemBox {
 	int32_t obj;
 	int32_t type; // rt_object_type of obj: the split shadow stage queues candidates by primitive kind without reading the object
 };
+// One scene-level leaf item again: what a float test in the primitive's OBJECT space needs (rt_prims.cuh: prim_miss_f) - the
+// 3x3 part of the object's inverse transform and the object-space position of a reference point (the centre of the item's
+// float box), both rounded to float.  A candidate whose box the ray enters but whose shape its line certainly misses - about
+// half of them for rotated boxes and cylinders, whose world boxes are loose - then costs this 64-byte record and ~60 float
+// instructions instead of the 248-byte rt_object, the world -> object transform in double precision and intersectLocal.
+// kind 0 = no such test for this item (trimesh, cone, a transform that is not rotation x uniform scale, degenerate numbers).
+enum { RT_PF_NONE = 0, RT_PF_BOX = 1, RT_PF_SPHERE = 2, RT_PF_CYLINDER = 3, RT_PF_SQUARE = 4 };
+struct alignas(64) DPrimF {
+	float m[9];  // row-major: object-space direction = m * world direction
+	float lc[3]; // object-space coordinates of the reference point, relative to the centre of the shape's own bounding box
+	int32_t kind;
+	int32_t pad[3];
+};
+
 // Shared-memory staging of the scene tree's top (north star item 1; A/B in profiles/r2_variants.txt): the first RT_TOP_K internal
 // nodes in BREADTH-FIRST order (the arrays are pre-order, so the top levels are not contiguous) as a table of DNode2f whose child
 // references to other table entries carry RT_REF_TOP | table index; pad[0] = the node's index in snodes2 (for the double boxes).
@@ -71,6 +85,7 @@ struct DScene {
 	const DNode2f* snodes2f; // float images, same indexing
 	const DNode2f* mnodes2f;
 	const DItemBox* sboxf;   // per scene leaf item
+	const DPrimF* sprimf;    // per scene leaf item (same index)
 	const DNode2f* stop;     // top table of the scene tree (RT_TOP_K entries, n_top used); see RT_REF_TOP
 	int32_t n_top;
 	int32_t pad_top_;

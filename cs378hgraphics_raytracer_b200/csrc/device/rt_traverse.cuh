@@ -451,15 +451,19 @@ RT_COLD int walk_enter_mesh(const DScene& S, Walk& W, const LocalRay& L, int fir
 template <int FIXED_MODE> RT_COLD int walk_leaf_items(const DScene& S, Walk& W, int first, int count, unsigned pend, RayF& F, const DNode2f*& nodesf, float& limf, int& level, int& sp, StackEnt* stk)
 {
 	const int mode = FIXED_MODE >= 0 ? FIXED_MODE : W.mode;
+	const unsigned sure = pend >> 8; // the float test already proved the double test's "hit" (boxf, result 1)
+	pend &= 0xffu;
 	unsigned keep = 0;
 #pragma unroll 1
 	while (pend) {
 		const int i = rt_ffs(pend) - 1;
 		pend &= pend - 1;
-		const rt_object& ob = S.objs[S.sboxf[first + i].obj];
-		double eb;
-		if (!box_hit(ob.bbox, ob.bbox + 3, W.o, W.d, W.I, eb)) continue;
-		if (W.prune && eb > W.lim) continue;
+		if (!((sure >> i) & 1u)) {
+			const rt_object& ob = S.objs[S.sboxf[first + i].obj];
+			double eb;
+			if (!box_hit(ob.bbox, ob.bbox + 3, W.o, W.d, W.I, eb)) continue;
+			if (W.prune && eb > W.lim) continue;
+		}
 		keep |= 1u << i;
 	}
 	int next = RT_REF_NONE;
@@ -468,7 +472,11 @@ template <int FIXED_MODE> RT_COLD int walk_leaf_items(const DScene& S, Walk& W, 
 		const int i = rt_ffs(keep) - 1;
 		keep &= keep - 1;
 		const int rank = first + i;
-		const int obj = S.sboxf[rank].obj;
+		const DItemBox& ib = S.sboxf[rank];
+		// object-space float test: a line that certainly misses the shape (rotated boxes and cylinders fill their world
+		// boxes badly) never reaches the object record or the double-precision code
+		if (ib.type != RT_OBJ_TRIMESH && prim_miss_f(S.sprimf[rank], ib, W.o, W.d)) continue;
+		const int obj = ib.obj;
 		const rt_object& ob = S.objs[obj];
 		LocalRay L;
 		to_local(L, ob, W.o, W.d);
@@ -585,11 +593,16 @@ RT_HD bool traverse(const DScene& S, const d3& ow, const d3& dw, const int mode_
 			} else {
 				// float images of the candidates' boxes first (32 bytes each): what is certainly missed, or
 				// certainly entered beyond the limit, never reaches the double-precision code
+				// (bit i: candidate i is pending; bit 8 + i: its box is CERTAINLY hit, the double test of the box is not needed)
 				unsigned pend = 0;
 #pragma unroll 1
 				for (int i = 0; i < count; i++) {
 					RT_CNT(objs, mode);
-					if (!box_miss_f(S.sboxf[first + i], F, prune ? limf : INFINITY)) pend |= 1u << i;
+					const DItemBox& ib = S.sboxf[first + i];
+					float e;
+					const int r = boxf(ib.lo, ib.hi, F, e);
+					if (r == 0 || (r == 1 && prune && e > limf)) continue;
+					pend |= (r == 1 ? 0x101u : 1u) << i;
 				}
 				if (pend) cur = walk_leaf_items<FIXED_MODE>(S, W, first, count, pend, F, nodesf, limf, level, sp, stk);
 			}

@@ -77,7 +77,7 @@ namespace {
 
 enum { B_ACCUM = 0, B_ACCUM2, B_POOL_D, B_POOL_I, B_SMALL, B_FB, B_XS, B_YS, B_REG_A, B_REG_B, B_PIXACC, B_RAYS, B_HITS,
        B_WQ0_D, B_WQ0_I, B_WQ1_D, B_WQ1_I, B_WSP_D, B_WSP_I, B_SQ_D, B_SQ_I, B_WH_T, B_WH_OF, B_HEAVY, B_RETRY, B_SQ2_D, B_SQ2_I,
-       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_CX_A, B_CX_B, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_STOP, B_BASE, B_BASE2, B_COUNT };
+       B_SK_A, B_SK_B, B_SI_A, B_SI_B, B_CK, B_CI, B_CX_A, B_CX_B, B_ARENA, B_SNODES2, B_MNODES2, B_SNODES2F, B_MNODES2F, B_SBOXF, B_MTREES, B_TRIS, B_MSLACK, B_PRE_S, B_PRE_M, B_TMP_A, B_TMP_B, B_TMP_C, B_TMP_D, B_CUBTMP, B_CUBTMP2, B_CUBTMP3, B_PACKED, B_STOP, B_BASE, B_BASE2, B_SPRIMF, B_COUNT };
 static_assert(B_COUNT <= 64, "rt_ctx::buf too small");
 
 #define CK(call)                                                                                          \
@@ -682,8 +682,9 @@ static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes,
 			k_derive_tris<<<blocks_for(n_mitems, 256), 256, 0, ctx->stream>>>(S.meshes, n_mesh, S.mitems, S.faces, S.verts, n_mitems, (DTri*)ctx->buf[B_TRIS], flags);
 	}
 	if ((st = ensure(ctx, B_SBOXF, (size_t)(n_sitems > 0 ? n_sitems : 1) * sizeof(DItemBox))) != RT_OK) return st;
+	if ((st = ensure(ctx, B_SPRIMF, (size_t)(n_sitems > 0 ? n_sitems : 1) * sizeof(DPrimF))) != RT_OK) return st;
 	if (n_sitems > 0) {
-		k_derive_itembox<<<blocks_for(n_sitems, 256), 256, 0, ctx->stream>>>(S.sitems, n_sitems, S.objs, (long long)A.count(RT_SEC_OBJECTS), (DItemBox*)ctx->buf[B_SBOXF]);
+		k_derive_itembox<<<blocks_for(n_sitems, 256), 256, 0, ctx->stream>>>(S.sitems, n_sitems, S.objs, (long long)A.count(RT_SEC_OBJECTS), (DItemBox*)ctx->buf[B_SBOXF], (DPrimF*)ctx->buf[B_SPRIMF]);
 		ctx->launches++;
 	}
 	{
@@ -697,6 +698,7 @@ static rt_status upload_scene_impl(rt_ctx* ctx, const void* arena, size_t bytes,
 	S.snodes2f = (const DNode2f*)ctx->buf[B_SNODES2F];
 	S.mnodes2f = (const DNode2f*)ctx->buf[B_MNODES2F];
 	S.sboxf = (const DItemBox*)ctx->buf[B_SBOXF];
+	S.sprimf = (const DPrimF*)ctx->buf[B_SPRIMF];
 	S.stop = nullptr;
 	S.n_top = 0;
 	S.pad_top_ = 0;
@@ -765,6 +767,7 @@ rt_status rt_selftest_derive(rt_ctx* ctx, const void* arena, size_t bytes, unsig
 	if ((st = cmp(ctx->S.snodes2f, D.snodes2f.data(), D.snodes2f.size() * sizeof(DNode2f))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.mnodes2f, D.mnodes2f.data(), D.mnodes2f.size() * sizeof(DNode2f))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.sboxf, D.sboxf.data(), D.sboxf.size() * sizeof(DItemBox))) != RT_OK) return st;
+	if ((st = cmp(ctx->S.sprimf, D.sprimf.data(), D.sprimf.size() * sizeof(DPrimF))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.mtrees, D.mtrees.data(), D.mtrees.size() * sizeof(DTree))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.tris, D.tris.data(), D.tris.size() * sizeof(DTri))) != RT_OK) return st;
 	if ((st = cmp(ctx->S.mesh_slack, D.mesh_slack.data(), D.mesh_slack.size() * sizeof(double))) != RT_OK) return st;

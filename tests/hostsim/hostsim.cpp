@@ -31,6 +31,7 @@ void setup(Sim& sim, const void* arena)
 	S.snodes2f = sim.D.snodes2f.data();
 	S.mnodes2f = sim.D.mnodes2f.data();
 	S.sboxf = sim.D.sboxf.data();
+	S.sprimf = sim.D.sprimf.data();
 	S.mtrees = sim.D.mtrees.data();
 	S.snodes = A.ptr<rt_node>(RT_SEC_SCENE_NODES);
 	S.sitems = A.ptr<int32_t>(RT_SEC_SCENE_ITEMS);
@@ -272,6 +273,65 @@ double sim_acc_read(const double* added, int n_added, const double* stored, int 
 	std::vector<double> base(3 * (size_t)lenses, 0.0);
 	for (int l = 0; l < lenses; l++) base[3 * l] = stored[l];
 	return acc_read3(acc, lenses ? base.data() : nullptr, lenses, 0).x;
+}
+
+// Soundness of the object-space float pre-test (rt_prims.cuh: prim_miss_f), brute force: every ray against every scene-level
+// item.  out[0] = pairs whose box the reference's double test enters, out[1] = of those, pairs the pre-test rejects,
+// out[2] = of those, pairs whose double-precision object-space test HITS (must be 0), out[3] = pairs with a pre-test at all
+// (kind != 0) among out[0], out[4] = pairs that hit, out[5] = rejected pairs over ALL items (box entered or not) that hit (must be 0).
+// aimed != 0: the direction of every (ray, item) pair is replaced by one from the ray's origin through a pseudo-random point of
+// the item's box enlarged by a fifth - every pair is then a hit or a near miss (grazing lines, corners, rims).
+int sim_primf_check(const void* arena, const double* rays, int n, int aimed, unsigned long long* out)
+{
+	Sim sim;
+	setup(sim, arena);
+	const DScene& S = sim.S;
+	const long long n_items = (long long)sim.D.sboxf.size();
+	unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0;
+#pragma omp parallel for schedule(dynamic, 16) reduction(+ : c0, c1, c2, c3, c4, c5)
+	for (int k = 0; k < n; k++) {
+		const d3 o = mk3(rays[6 * k], rays[6 * k + 1], rays[6 * k + 2]);
+		d3 d = mk3(rays[6 * k + 3], rays[6 * k + 4], rays[6 * k + 5]);
+		RayInv I;
+		RayF F;
+		make_inv(I, F, o, d, 0.0, S.scene_slack * 1e9);
+		for (long long r = 0; r < n_items; r++) {
+			const DItemBox& ib = S.sboxf[r];
+			const rt_object& ob = S.objs[ib.obj];
+			if (ob.type == RT_OBJ_TRIMESH) continue;
+			if (aimed) {
+				unsigned long long hsh = (unsigned long long)k * 0x9E3779B97F4A7C15ull + (unsigned long long)r * 0xC2B2AE3D27D4EB4Full + 12345u;
+				double u[3];
+				for (int c = 0; c < 3; c++) {
+					hsh ^= hsh >> 29; hsh *= 0xBF58476D1CE4E5B9ull; hsh ^= hsh >> 32;
+					u[c] = ((double)(hsh >> 11) / 9007199254740992.0 * 2.0 - 1.0) * 1.2;
+				}
+				const double cx = 0.5 * (ob.bbox[0] + ob.bbox[3]), cy = 0.5 * (ob.bbox[1] + ob.bbox[4]), cz = 0.5 * (ob.bbox[2] + ob.bbox[5]);
+				d = mk3(cx + u[0] * 0.5 * (ob.bbox[3] - ob.bbox[0]) - o.x, cy + u[1] * 0.5 * (ob.bbox[4] - ob.bbox[1]) - o.y, cz + u[2] * 0.5 * (ob.bbox[5] - ob.bbox[2]) - o.z);
+				if (aimed == 2) d = normalize(d);
+				make_inv(I, F, o, d, 0.0, S.scene_slack * 1e9);
+			}
+			const bool miss = prim_miss_f(S.sprimf[r], ib, o, d);
+			LocalRay L;
+			to_local(L, ob, o, d);
+			TravClosest C;
+			C.have = false;
+			C.best_t = RT_T_INF;
+			C.best_rank = 0x7fffffff;
+			C.best_obj = -1;
+			C.best_fpos = -1;
+			prim_closest(ob, L, (int)r, ib.obj, C);
+			if (miss && C.have) c5++;
+			double eb;
+			if (!box_hit(ob.bbox, ob.bbox + 3, o, d, I, eb)) continue;
+			c0++;
+			if (S.sprimf[r].kind != RT_PF_NONE) c3++;
+			if (C.have) c4++;
+			if (miss) { c1++; if (C.have) c2++; }
+		}
+	}
+	out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3; out[4] = c4; out[5] = c5;
+	return 0;
 }
 
 } // extern "C"

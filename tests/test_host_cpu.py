@@ -425,3 +425,30 @@ def test_colour_accumulator_limbs(hostsim):
         assert got == want
     one = np.array([0.6])
     assert hostsim.sim_acc_read(None, 0, one.ctypes.data, 1) == 0.6  # a camera ray that hits a flat emitter: that very double
+
+
+def test_object_space_float_pretest_is_sound(rtlib, hostsim, scene_dir):
+    """csrc/device/rt_prims.cuh: prim_miss_f skips the double-precision object-space test of a scene-level candidate when its
+    float test proves that the ray's line misses the shape.  Brute force on the host build: every ray against every item,
+    with the given directions and with directions aimed through a random point of each item's slightly enlarged box (so
+    that every pair is a hit or a near miss), origins far outside (1000 x the extent) and inside the scene: no pair the
+    double-precision test hits is ever rejected; on the rotated boxes / cylinders / spheres of the mixed scene the test
+    removes most of the misses among the candidates whose box is entered."""
+    hostsim.sim_primf_check.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    rng = np.random.default_rng(21)
+    for name, extent, n in (("mixed_small.ray", 200.0, 400), ("hitchcock.ray", 6.0, 6000), ("prims_mixed.ray", 8.0, 6000),
+                            ("lights_area.ray", 8.0, 3000)):
+        arena = rtlib.load_ray_file(str(scene_dir / name))
+        o = rng.uniform(-1.5 * extent, 1.5 * extent, (n, 3))
+        o[:n // 8] *= 1e3
+        o[n // 8:n // 4] *= 0.05
+        d = rng.normal(size=(n, 3))
+        d[n // 2:n // 2 + n // 10] = np.eye(3)[rng.integers(0, 3, n // 10)]  # zero components
+        rays = np.ascontiguousarray(np.hstack([o, d]))
+        for aimed in (0, 1, 2):
+            out = (ctypes.c_uint64 * 6)()
+            assert hostsim.sim_primf_check(ctypes.c_void_p(arena.ptr), rays.ctypes.data, n, aimed, out) == 0
+            entered, rejected, bad, with_test, hits, bad_all = list(out)
+            assert bad == 0 and bad_all == 0, (name, aimed, list(out))
+            if aimed and name == "mixed_small.ray":
+                assert with_test == entered and rejected > 0.9 * (entered - hits), list(out)
